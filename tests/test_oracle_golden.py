@@ -1,0 +1,72 @@
+"""Pins the CPU oracle against the reference's own golden numbers:
+quadrature tables and the OC compliance trajectories logged by the authors' runs."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, MATERIAL, bc_path
+
+TRAJ = json.load(open(os.path.join(GOLDEN, "oc_trajectories.json")))
+
+
+def test_quadrature_tables(oracle_mod):
+    """VoxelFEM/tests/test_tp_gauss_quadrature.cc:44-73: every rule integrates every monomial it should to 5e-16."""
+    O = oracle_mod
+    q = json.load(open(os.path.join(GOLDEN, "quadrature_goldens.json")))
+    ntests = 0
+    for nv in (1, 2, 3):
+        tab = q["%dvar" % nv]
+        for (num, den), degs in zip(tab["integrals_num_den"], tab["degrees"]):
+            exact = num / den
+            # all rules with per-axis degree 0..9 that can integrate this monomial exactly
+            for rule in ([max(d, 0) for d in degs], [9] * nv, [min(d + 1, 9) for d in degs]):
+                val = O.gauss_monomial(rule, degs)
+                assert abs(val - exact) <= 5e-16, (degs, rule, val, exact)
+                ntests += 1
+    assert ntests > 3000
+
+
+def _setup_2d(O, log, bc, dom, grid, vol):
+    s = O.OracleSim([0, 0], dom, grid)
+    s.read_material(MATERIAL)
+    s.set_densities(np.full(s.ne, vol))
+    s.apply_bc_file(bc_path(bc))
+    s.set_simp(1.0, 1e-4, 3.0)
+    s.top_create(False, vol, [("smoothing", 1), ("projection", 1.0)])
+    s.top_set_vars(s.densities())
+    return s
+
+
+@pytest.mark.parametrize("log,bc,dom,grid,vol,nsteps", [
+    ("2dMbb300x100", "2d/mbb_beam.bc", [3, 1], [300, 100], 0.3, 3),
+    ("2dBridge250x125", "2d/bridge.bc", [2, 1], [250, 125], 0.4, 2),
+])
+def test_direct_solve_oc_trajectory(oracle_mod, log, bc, dom, grid, vol, nsteps):
+    """logs/slurm/gt/<log>.log: `--mgl 0` runs (CHOLMOD direct solve), filters [Smoothing r=1, Projection beta=1],
+    OC(m=0.2, ctol=1e-6).  Compliance is printed with 6 decimals, the OC line with 6 significant digits."""
+    gold = TRAJ[log]
+    cfg = eval(gold["config"])
+    assert cfg["gridDimensions"] == grid and cfg["domainCorners"][1] == dom and cfg["maxVolume"] == [vol]
+    s = _setup_2d(oracle_mod, log, bc, dom, grid, vol)
+    for k in range(nsteps + 1):
+        c = 2.0 * s.top_objective()
+        assert abs(c - gold["compliance"][k]) <= 2e-9 * gold["compliance"][k] + 1e-6, (k, c, gold["compliance"][k])
+        if k == nsteps:
+            break
+        lam, _ = s.oc_step()
+        J, cv, lg = gold["oc_lines_head"][k]
+        assert abs(s.top_objective() - J) <= 1e-5 * J
+        assert abs(lam - lg) <= 1e-5 * lg
+        assert abs(s.top_constraint() - cv) <= 2e-9  # printed with 6 significant digits of a ~1e-7 number
+
+
+@pytest.mark.slow
+def test_direct_solve_oc_trajectory_50_steps(oracle_mod):
+    gold = TRAJ["2dMbb300x100"]
+    s = _setup_2d(oracle_mod, "2dMbb300x100", "2d/mbb_beam.bc", [3, 1], [300, 100], 0.3)
+    for k in range(51):
+        c = 2.0 * s.top_objective()
+        assert abs(c - gold["compliance"][k]) <= 1e-7 * gold["compliance"][k], (k, c, gold["compliance"][k])
+        s.oc_step()
