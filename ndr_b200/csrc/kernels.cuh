@@ -1,0 +1,242 @@
+// ndr_b200 — CUDA kernels of the elasticity solve (sm_100a, FP64).
+//
+// Every kernel here is a gather: one thread owns one output node (or one stencil block) and
+// reads its 3^N neighbourhood, so no atomics are needed and results are deterministic.
+// Reference semantics (cited per kernel): TPS.hh = VoxelFEM/TensorProductSimulator.hh,
+// MG.hh = VoxelFEM/MultigridSolver.hh.
+#pragma once
+#include "common.h"
+
+namespace vfem {
+
+constexpr int kBlock = 128;
+
+// ---- index helpers --------------------------------------------------------------------------
+template <int N>
+__device__ __forceinline__ void unflattenNode(const Grid<N> &g, int n, int *idx) {
+#pragma unroll
+    for (int d = N - 1; d > 0; --d) { int q = n / g.n[d]; idx[d] = n - q * g.n[d]; n = q; }
+    idx[0] = n;
+}
+template <int N>
+__device__ __forceinline__ int flattenNode(const Grid<N> &g, const int *idx) {
+    int r = 0;
+#pragma unroll
+    for (int d = 0; d < N; ++d) r += idx[d] * g.ninc[d];
+    return r;
+}
+// thread t of colour lattice `par` (idx_d = par_d + 2*k_d); returns false when t is out of range
+template <int N>
+__device__ __forceinline__ bool colourNode(const Grid<N> &g, int t, int colour, int *idx) {
+    int cnt[N];
+#pragma unroll
+    for (int d = 0; d < N; ++d) { int par = (colour >> (N - 1 - d)) & 1; cnt[d] = (g.n[d] - 1 - par) / 2 + 1; }
+#pragma unroll
+    for (int d = N - 1; d > 0; --d) { int q = t / cnt[d]; idx[d] = ((colour >> (N - 1 - d)) & 1) + 2 * (t - q * cnt[d]); t = q; }
+    idx[0] = ((colour >> (N - 1)) & 1) + 2 * t;
+    return t < cnt[0];
+}
+template <int N>
+inline int colourCount(const Grid<N> &g, int colour) {
+    long long tot = 1;
+    for (int d = 0; d < N; ++d) { int par = (colour >> (N - 1 - d)) & 1; tot *= (g.n[d] - 1 - par) / 2 + 1; }
+    return int(tot);
+}
+
+// ---- fine level, matrix-free: row n of K(rho) u ------------------------------------------------
+// acc[c] += sum_{e incident to n} E_e * K0[(loc_e(n), c), :] . u_e      (TPS.hh:933-951 gathered per
+// node; the same row is what MG.hh:205-222 subtracts from b in the smoother).
+// M (optional) = sum_e E_e * K0[(loc,:),(loc,:)], the node's diagonal block (MG.hh:223-225).
+// Out-of-grid neighbours read 0 and out-of-grid elements get modulus 0: branch-free, and
+// adding exact zeros leaves the result unchanged.
+template <int N, bool WITH_M>
+__device__ __forceinline__ void fineNodeRow(const Grid<N> &g, const K0Param<N> &K, const Real *__restrict__ Ey,
+                                            const Real *__restrict__ u, const int *idx, Real *acc, Real *M) {
+    constexpr int NPE = 1 << N, KS = N * NPE, NST = ipow3(N);
+    Real un[NST][N];
+#pragma unroll
+    for (int k = 0; k < NST; ++k) {
+        int t = k, off = 0; bool ok = true;
+#pragma unroll
+        for (int d = N - 1; d >= 0; --d) {
+            int dl = t % 3 - 1; t /= 3;
+            int v = idx[d] + dl; ok = ok && (v >= 0) && (v < g.n[d]);
+            off += dl * g.ninc[d];
+        }
+        int base = flattenNode<N>(g, idx) + off;
+#pragma unroll
+        for (int c = 0; c < N; ++c) un[k][c] = ok ? u[size_t(base) * N + c] : 0.0;
+    }
+#pragma unroll
+    for (int s = 0; s < NPE; ++s) {
+        int ei = 0, loc = 0; bool ok = true;
+#pragma unroll
+        for (int d = 0; d < N; ++d) {
+            int sd = (s >> (N - 1 - d)) & 1;
+            int e = idx[d] - 1 + sd; ok = ok && (e >= 0) && (e < g.E[d]);
+            ei += e * g.einc[d];
+            loc |= (1 - sd) << (N - 1 - d);
+        }
+        const Real Ee = ok ? Ey[ei] : 0.0;
+        Real r[N];
+#pragma unroll
+        for (int c = 0; c < N; ++c) r[c] = 0.0;
+#pragma unroll
+        for (int q = 0; q < NPE; ++q) {
+            int k = 0; // neighbourhood slot of local node q of incident element s
+#pragma unroll
+            for (int d = 0; d < N; ++d) {
+                int sd = (s >> (N - 1 - d)) & 1, qd = (q >> (N - 1 - d)) & 1;
+                k = k * 3 + (sd - 1 + qd + 1);
+            }
+#pragma unroll
+            for (int b = 0; b < N; ++b)
+#pragma unroll
+                for (int c = 0; c < N; ++c) r[c] = fma(K.k[(loc * N + c) * KS + q * N + b], un[k][b], r[c]);
+        }
+#pragma unroll
+        for (int c = 0; c < N; ++c) acc[c] = fma(Ee, r[c], acc[c]);
+        if (WITH_M) {
+#pragma unroll
+            for (int c = 0; c < N; ++c)
+#pragma unroll
+                for (int c2 = 0; c2 < N; ++c2) M[c * N + c2] = fma(Ee, K.k[(loc * N + c) * KS + loc * N + c2], M[c * N + c2]);
+        }
+    }
+}
+
+// ---- coarse levels: assembled 3^N-point block stencil ---------------------------------------------
+// S[(k*N*N + a*N + b) * nn + n] = K_l[(n,a), (n + delta(k), b)] (zero for out-of-grid neighbours).
+// The reference stores the same operator as a block-CSC matrix (TPS.hh:649-720) and applies it
+// with applyTransposeParallel (SparseMatrices.hh:1519-1568).
+template <int N, bool WITH_M>
+__device__ __forceinline__ void stencilNodeRow(const Grid<N> &g, const Real *__restrict__ S, const Real *__restrict__ u,
+                                               const int *idx, int n, Real *acc, Real *M) {
+    constexpr int NST = ipow3(N);
+#pragma unroll
+    for (int k = 0; k < NST; ++k) {
+        int t = k, off = 0; bool ok = true;
+#pragma unroll
+        for (int d = N - 1; d >= 0; --d) {
+            int dl = t % 3 - 1; t /= 3;
+            int v = idx[d] + dl; ok = ok && (v >= 0) && (v < g.n[d]);
+            off += dl * g.ninc[d];
+        }
+        Real um[N];
+#pragma unroll
+        for (int b = 0; b < N; ++b) um[b] = ok ? u[size_t(n + off) * N + b] : 0.0;
+#pragma unroll
+        for (int a = 0; a < N; ++a)
+#pragma unroll
+            for (int b = 0; b < N; ++b) {
+                Real s = S[size_t(k * N * N + a * N + b) * g.nn + n];
+                acc[a] = fma(s, um[b], acc[a]);
+                if (WITH_M && k == NST / 2) M[a * N + b] = s;
+            }
+    }
+}
+
+// Gauss-Seidel update of one node (MG.hh:248-264): t = b_n - (K u)_n, then one component-wise
+// forward/backward substitution through the diagonal block M; constrained components get 0.
+template <int N>
+__device__ __forceinline__ void gsNodeUpdate(const Real *t, const Real *M, unsigned mask, bool forward, Real *__restrict__ u, int n) {
+    Real du[N];
+#pragma unroll
+    for (int c = 0; c < N; ++c) du[c] = 0.0;
+#pragma unroll
+    for (int ii = 0; ii < N; ++ii) {
+        const int i = forward ? ii : (N - 1 - ii);
+        Real s = 0.0;
+#pragma unroll
+        for (int j = 0; j < N; ++j) s = fma(M[i * N + j], du[j], s);
+        const Real inv = ((mask >> i) & 1u) ? 0.0 : 1.0 / M[i * N + i];
+        du[i] = (t[i] - s) * inv;
+    }
+#pragma unroll
+    for (int c = 0; c < N; ++c) u[size_t(n) * N + c] += du[c];
+}
+
+// ---- K u / residual kernels ---------------------------------------------------------------------
+// MODE 0: out = K u (TPS.hh:905-952, MG.hh:353-358)
+// MODE 1: out = mask(b - K u)     (MG::computeResidual, MG.hh:401-413)
+// MODE 2: out = mask(K u)         (PCG's A d, MG.hh:719-720)
+template <int N, int MODE>
+__global__ void __launch_bounds__(kBlock) applyFineKernel(Grid<N> g, K0Param<N> K, const Real *__restrict__ Ey,
+                                                           const Real *__restrict__ u, const Real *__restrict__ b,
+                                                           const uint8_t *__restrict__ dmask, Real *__restrict__ out) {
+    int n = blockIdx.x * kBlock + threadIdx.x;
+    if (n >= g.nn) return;
+    int idx[N]; unflattenNode<N>(g, n, idx);
+    Real acc[N];
+#pragma unroll
+    for (int c = 0; c < N; ++c) acc[c] = 0.0;
+    fineNodeRow<N, false>(g, K, Ey, u, idx, acc, nullptr);
+    unsigned m = (MODE != 0) ? dmask[n] : 0u;
+#pragma unroll
+    for (int c = 0; c < N; ++c) {
+        Real v = (MODE == 1) ? b[size_t(n) * N + c] - acc[c] : acc[c];
+        if ((m >> c) & 1u) v = 0.0;
+        out[size_t(n) * N + c] = v;
+    }
+}
+
+template <int N, int MODE>
+__global__ void __launch_bounds__(kBlock) applyStencilKernel(Grid<N> g, const Real *__restrict__ S, const Real *__restrict__ u,
+                                                              const Real *__restrict__ b, const uint8_t *__restrict__ dmask,
+                                                              Real *__restrict__ out) {
+    int n = blockIdx.x * kBlock + threadIdx.x;
+    if (n >= g.nn) return;
+    int idx[N]; unflattenNode<N>(g, n, idx);
+    Real acc[N];
+#pragma unroll
+    for (int c = 0; c < N; ++c) acc[c] = 0.0;
+    stencilNodeRow<N, false>(g, S, u, idx, n, acc, nullptr);
+    unsigned m = (MODE != 0) ? dmask[n] : 0u;
+#pragma unroll
+    for (int c = 0; c < N; ++c) {
+        Real v = (MODE == 1) ? b[size_t(n) * N + c] - acc[c] : acc[c];
+        if ((m >> c) & 1u) v = 0.0;
+        out[size_t(n) * N + c] = v;
+    }
+}
+
+// ---- multicoloured Gauss-Seidel: one colour phase (MG.hh:284-340) --------------------------------
+template <int N>
+__global__ void __launch_bounds__(kBlock) gsFineKernel(Grid<N> g, K0Param<N> K, const Real *__restrict__ Ey, Real *__restrict__ u,
+                                                        const Real *__restrict__ b, const uint8_t *__restrict__ dmask, int colour,
+                                                        int forward) {
+    int t = blockIdx.x * kBlock + threadIdx.x;
+    int idx[N];
+    if (!colourNode<N>(g, t, colour, idx)) return;
+    int n = flattenNode<N>(g, idx);
+    Real acc[N], M[N * N];
+#pragma unroll
+    for (int c = 0; c < N; ++c) acc[c] = 0.0;
+#pragma unroll
+    for (int i = 0; i < N * N; ++i) M[i] = 0.0;
+    fineNodeRow<N, true>(g, K, Ey, u, idx, acc, M);
+    Real tt[N];
+#pragma unroll
+    for (int c = 0; c < N; ++c) tt[c] = b[size_t(n) * N + c] - acc[c];
+    gsNodeUpdate<N>(tt, M, dmask[n], forward != 0, u, n);
+}
+
+template <int N>
+__global__ void __launch_bounds__(kBlock) gsStencilKernel(Grid<N> g, const Real *__restrict__ S, Real *__restrict__ u,
+                                                           const Real *__restrict__ b, const uint8_t *__restrict__ dmask, int colour,
+                                                           int forward) {
+    int t = blockIdx.x * kBlock + threadIdx.x;
+    int idx[N];
+    if (!colourNode<N>(g, t, colour, idx)) return;
+    int n = flattenNode<N>(g, idx);
+    Real acc[N], M[N * N];
+#pragma unroll
+    for (int c = 0; c < N; ++c) acc[c] = 0.0;
+    stencilNodeRow<N, true>(g, S, u, idx, n, acc, M);
+    Real tt[N];
+#pragma unroll
+    for (int c = 0; c < N; ++c) tt[c] = b[size_t(n) * N + c] - acc[c];
+    gsNodeUpdate<N>(tt, M, dmask[n], forward != 0, u, n);
+}
+
+} // namespace vfem

@@ -1,0 +1,245 @@
+// ndr_b200 — MultigridSolver host logic: hierarchy setup, operator refresh, launches.
+#include "mg.h"
+#include "kernels.cuh"
+#include "kernels_mg.cuh"
+#include <cusolverDn.h>
+
+namespace vfem {
+
+static const size_t kMaxCoarseDofs = 12288; // dense inverse: 1.2 GB at the limit
+
+#define VFEM_CUSOLVER(call)                                                                              \
+    do {                                                                                                 \
+        cusolverStatus_t s_ = (call);                                                                    \
+        if (s_ != CUSOLVER_STATUS_SUCCESS)                                                               \
+            throw std::runtime_error("cuSOLVER error " + std::to_string(int(s_)) + " at " + __FILE__ + ":" + std::to_string(__LINE__)); \
+    } while (0)
+
+template <int N>
+MG<N>::MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels) : sim(fine) {
+    dim = N;
+    stream = fine->stream;
+    int E[N];
+    for (int d = 0; d < N; ++d) E[d] = fine->g.E[d];
+    lv.resize(numCoarseningLevels + 1);
+    for (size_t l = 0; l <= numCoarseningLevels; ++l) {
+        Level &L = lv[l];
+        if (l == 0) { L.g = fine->g; L.dmask = fine->dmask; }
+        else {
+            for (int d = 0; d < N; ++d) {
+                if (E[d] % 2 == 1)
+                    throw std::runtime_error("Grid size currently must be divisible by 2^numCoarseningLevels (nonuniform coarsening not yet implemented)"); // MG.hh:36-37
+                E[d] /= 2;
+            }
+            L.g = makeGrid<N>(E);
+            L.dmask.assign(L.g.nn, 0);
+            // Dirichlet coarsening (MG.hh:43-84): a fine constrained node lying on a coarse vertex /
+            // edge / face constrains, with the same component mask, every coarse node of that entity.
+            const Level &F = lv[l - 1];
+            for (int nf = 0; nf < F.g.nn; ++nf) {
+                const uint8_t m = F.dmask[nf];
+                if (!m) continue;
+                int fi[N], r = nf, lo[N], cnt[N]; bool interior = true;
+                for (int d = N - 1; d >= 0; --d) { fi[d] = r % F.g.n[d]; r /= F.g.n[d]; }
+                for (int d = 0; d < N; ++d) { lo[d] = fi[d] / 2; cnt[d] = (fi[d] & 1) ? 2 : 1; if (cnt[d] == 1) interior = false; }
+                if (interior) throw std::runtime_error("Dirichlet constraints on internal nodes are not supported"); // MG.hh:70
+                for (int j = 0; j < NPE; ++j) {
+                    int cn = 0; bool use = true;
+                    for (int d = 0; d < N; ++d) { int bit = (j >> (N - 1 - d)) & 1; if (bit >= cnt[d]) use = false; cn += (lo[d] + bit) * L.g.ninc[d]; }
+                    if (use) L.dmask[cn] |= m;
+                }
+            }
+            L.S.alloc(size_t(L.g.nn) * NST * N * N);
+            L.d_dval.alloc(size_t(L.g.nn) * N); L.d_dval.zero(stream);
+            L.d_dmask.upload(L.dmask, stream);
+        }
+        L.x.alloc(size_t(L.g.nn) * N); L.b.alloc(size_t(L.g.nn) * N); L.r.alloc(size_t(L.g.nn) * N);
+        L.x.zero(stream); L.b.zero(stream);
+    }
+    const size_t nd = levelDofs(0);
+    p_x.alloc(nd); p_r.alloc(nd); p_d.alloc(nd); p_Ad.alloc(nd); p_b.alloc(nd);
+    d_scal.alloc(8); d_scal.zero(stream);
+    d_partials.alloc(size_t(kRedMaxBlocks) * 4); d_ticket.alloc(1); d_ticket.zero(stream);
+    rw.partials = d_partials.p; rw.ticket = d_ticket.p;
+    VFEM_CUDA(cudaMallocHost((void **)&h_scal, 8 * sizeof(Real)));
+    d_C.alloc(size_t(NPE) * KS * KS);
+    d_info.alloc(1);
+    VFEM_CUDA(cudaStreamSynchronize(stream));
+}
+
+template <int N>
+MG<N>::~MG() {
+    if (h_scal) cudaFreeHost(h_scal);
+    if (cusolverHandle) cusolverDnDestroy((cusolverDnHandle_t)cusolverHandle);
+}
+
+template <int N>
+void MG<N>::syncMasks() {
+    sim->syncBC();
+}
+
+// C_fi = I_fi^T K0 I_fi with I_fi[(i,c),(J,d)] = phi_J(xi_i) delta_cd, xi_i the position of node i of
+// child fi inside the parent element (MG.hh:559-583, 644-648; child bit d <-> axis d).
+template <int N>
+static void coarsenedReferenceStiffness(const K0Param<N> &K0, std::vector<Real> &C) {
+    constexpr int NPE = 1 << N, KS = N * NPE;
+    C.assign(size_t(NPE) * KS * KS, 0.0);
+    for (int fi = 0; fi < NPE; ++fi) {
+        Real phi[NPE][NPE]; // [fine node i][coarse node J]
+        for (int i = 0; i < NPE; ++i)
+            for (int J = 0; J < NPE; ++J) {
+                Real v = 1.0;
+                for (int d = 0; d < N; ++d) {
+                    Real xi = 0.5 * ((i >> (N - 1 - d)) & 1) + 0.5 * ((fi >> d) & 1);
+                    v *= ((J >> (N - 1 - d)) & 1) ? xi : 1.0 - xi;
+                }
+                phi[i][J] = v;
+            }
+        Real *Cf = &C[size_t(fi) * KS * KS];
+        for (int J = 0; J < NPE; ++J)
+            for (int J2 = 0; J2 < NPE; ++J2)
+                for (int c = 0; c < N; ++c)
+                    for (int d = 0; d < N; ++d) {
+                        Real s = 0.0;
+                        for (int i = 0; i < NPE; ++i)
+                            for (int i2 = 0; i2 < NPE; ++i2) s += phi[i][J] * K0.k[(i * N + c) * KS + i2 * N + d] * phi[i2][J2];
+                        Cf[(J * N + c) * KS + J2 * N + d] = s;
+                    }
+    }
+}
+
+template <int N>
+void MG<N>::updateElementStiffnessMatrices(bool force) {
+    if (!force && builtVersion == sim->densityVersion) return;
+    const size_t L = lv.size() - 1;
+    if (L == 0) throw std::runtime_error("multigridSolver: at least one coarsening level is required on the device path");
+    const Real *Ey = sim->moduli();
+    std::vector<Real> C; coarsenedReferenceStiffness<N>(sim->K0, C);
+    d_C.upload(C, stream);
+    {
+        long long tot = (long long)lv[1].g.nn * NST;
+        buildLevel1StencilKernel<N><<<unsigned((tot + kBlock - 1) / kBlock), kBlock, 0, stream>>>(lv[0].g, lv[1].g, Ey, d_C.p, lv[1].S.p);
+        VFEM_CHECK_LAUNCH(); countLaunch();
+    }
+    for (size_t l = 2; l <= L; ++l) {
+        long long tot = (long long)lv[l].g.nn * NST;
+        galerkinStencilKernel<N><<<unsigned((tot + kBlock - 1) / kBlock), kBlock, 0, stream>>>(lv[l - 1].g, lv[l].g, lv[l - 1].S.p, lv[l].S.p);
+        VFEM_CHECK_LAUNCH(); countLaunch();
+    }
+    // coarsest level: dense inverse of the Dirichlet-reduced operator
+    const Level &Lc = lv[L];
+    const size_t nd = size_t(Lc.g.nn) * N;
+    if (nd > kMaxCoarseDofs)
+        throw std::runtime_error("coarsest multigrid level has " + std::to_string(nd) + " dofs; the device path solves it through a dense inverse "
+                                 "and needs <= " + std::to_string(kMaxCoarseDofs) + " (use more coarsening levels)");
+    coarseDofs = int(nd);
+    d_Ainv.alloc(nd * nd);
+    d_Ainv.zero(stream);
+    {
+        long long tot = (long long)Lc.g.nn * NST;
+        assembleDenseKernel<N><<<unsigned((tot + kBlock - 1) / kBlock), kBlock, 0, stream>>>(Lc.g, Lc.S.p, Lc.d_dmask.p, d_Ainv.p);
+        VFEM_CHECK_LAUNCH(); countLaunch();
+    }
+    if (!cusolverHandle) {
+        cusolverDnHandle_t hnd;
+        VFEM_CUSOLVER(cusolverDnCreate(&hnd));
+        cusolverHandle = hnd;
+    }
+    cusolverDnHandle_t hnd = (cusolverDnHandle_t)cusolverHandle;
+    VFEM_CUSOLVER(cusolverDnSetStream(hnd, stream));
+    int lw1 = 0, lw2 = 0;
+    VFEM_CUSOLVER(cusolverDnDpotrf_bufferSize(hnd, CUBLAS_FILL_MODE_LOWER, int(nd), d_Ainv.p, int(nd), &lw1));
+    VFEM_CUSOLVER(cusolverDnDpotri_bufferSize(hnd, CUBLAS_FILL_MODE_LOWER, int(nd), d_Ainv.p, int(nd), &lw2));
+    const int lw = lw1 > lw2 ? lw1 : lw2;
+    if (d_solverWork.n < size_t(lw)) d_solverWork.alloc(size_t(lw));
+    VFEM_CUSOLVER(cusolverDnDpotrf(hnd, CUBLAS_FILL_MODE_LOWER, int(nd), d_Ainv.p, int(nd), d_solverWork.p, lw, d_info.p));
+    int info = 0;
+    VFEM_CUDA(cudaMemcpyAsync(&info, d_info.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    VFEM_CUDA(cudaStreamSynchronize(stream));
+    if (info != 0) throw std::runtime_error("Cholesky factorization failed: coarsest-level matrix not positive definite (info " + std::to_string(info) + ")");
+    VFEM_CUSOLVER(cusolverDnDpotri(hnd, CUBLAS_FILL_MODE_LOWER, int(nd), d_Ainv.p, int(nd), d_solverWork.p, lw, d_info.p));
+    {
+        dim3 blk(32, 8), grd(unsigned((nd + 31) / 32), unsigned((nd + 7) / 8));
+        symmetrizeKernel<<<grd, blk, 0, stream>>>(d_Ainv.p, int(nd));
+        VFEM_CHECK_LAUNCH(); countLaunch();
+    }
+    builtVersion = sim->densityVersion;
+}
+
+template <int N>
+void MG<N>::coarseSolve(const Real *b, Real *x) {
+    const Level &Lc = lv.back();
+    const int nd = coarseDofs;
+    const int threads = 128, rowsPerBlock = threads / 32;
+    denseSolveKernel<N><<<(nd + rowsPerBlock - 1) / rowsPerBlock, threads, 0, stream>>>(d_Ainv.p, b, Lc.d_dmask.p, x, nd);
+    VFEM_CHECK_LAUNCH(); countLaunch();
+}
+
+// ---- per-level operators ------------------------------------------------------------------------------
+template <int N>
+static inline const uint8_t *maskOf(MG<N> &mg, size_t l) { return l == 0 ? mg.sim->d_dmask.p : mg.lv[l].d_dmask.p; }
+template <int N>
+static inline const Real *dvalOf(MG<N> &mg, size_t l) { return l == 0 ? mg.sim->d_dval.p : mg.lv[l].d_dval.p; }
+
+template <int N>
+template <int MODE>
+void MG<N>::applyMode(size_t l, const Real *u, const Real *b, Real *out) {
+    const Level &L = lv.at(l);
+    const unsigned blocks = unsigned((L.g.nn + kBlock - 1) / kBlock);
+    if (l == 0) {
+        const Real *Ey = sim->moduli();
+        applyFineKernel<N, MODE><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), out);
+    } else {
+        applyStencilKernel<N, MODE><<<blocks, kBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), out);
+    }
+    VFEM_CHECK_LAUNCH(); countLaunch();
+}
+
+template <int N> void MG<N>::applyK(size_t l, const Real *u, Real *out) { applyMode<0>(l, u, nullptr, out); }
+template <int N> void MG<N>::computeResidual(size_t l, const Real *u, const Real *b, Real *r) { applyMode<1>(l, u, b, r); }
+template <int N> void MG<N>::applyKMasked(size_t l, const Real *u, Real *out) { applyMode<2>(l, u, nullptr, out); }
+
+template <int N>
+void MG<N>::smoothColoured(size_t l, Real *u, const Real *b, bool forward) {
+    const Level &L = lv.at(l);
+    const Real *Ey = (l == 0) ? sim->moduli() : nullptr;
+    for (int i = 0; i < NPE; ++i) {
+        const int colour = forward ? i : NPE - 1 - i; // MG.hh:318-320
+        const int cnt = colourCount<N>(L.g, colour);
+        const unsigned blocks = unsigned((cnt + kBlock - 1) / kBlock);
+        if (l == 0) gsFineKernel<N><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
+        else gsStencilKernel<N><<<blocks, kBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), colour, forward ? 1 : 0);
+        VFEM_CHECK_LAUNCH(); countLaunch();
+    }
+}
+
+template <int N>
+void MG<N>::restriction(size_t lf, const Real *vf, Real *bc) {
+    const Level &F = lv.at(lf), &C = lv.at(lf + 1);
+    restrictKernel<N><<<(C.g.nn + kBlock - 1) / kBlock, kBlock, 0, stream>>>(F.g, C.g, vf, bc);
+    VFEM_CHECK_LAUNCH(); countLaunch();
+}
+
+template <int N>
+void MG<N>::interpolate(size_t lf, const Real *xc, Real *xf, bool accumulate) {
+    const Level &F = lv.at(lf), &C = lv.at(lf + 1);
+    const unsigned blocks = unsigned((F.g.nn + kBlock - 1) / kBlock);
+    if (accumulate) prolongKernel<N, true><<<blocks, kBlock, 0, stream>>>(F.g, C.g, xc, xf);
+    else prolongKernel<N, false><<<blocks, kBlock, 0, stream>>>(F.g, C.g, xc, xf);
+    VFEM_CHECK_LAUNCH(); countLaunch();
+}
+
+template <int N>
+void MG<N>::enforceDirichlet(size_t l, Real *u, bool zero) {
+    const size_t n = levelDofs(l);
+    enforceDirichletKernel<N><<<reduceBlocks(n), kRedBlock, 0, stream>>>(u, maskOf(*this, l), dvalOf(*this, l), n, zero ? 1 : 0);
+    VFEM_CHECK_LAUNCH(); countLaunch();
+}
+template <int N> void MG<N>::zeroOutDirichlet(size_t l, Real *u) { enforceDirichlet(l, u, true); }
+
+#include "mg_cycles.inl"
+
+template struct MG<2>;
+template struct MG<3>;
+
+} // namespace vfem

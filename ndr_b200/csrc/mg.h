@@ -1,0 +1,85 @@
+// ndr_b200 — geometric multigrid + MG-preconditioned CG, device resident.
+// Mirrors MultigridSolver<1,...> (VoxelFEM/MultigridSolver.hh:11-759).
+//
+// Design (not a port): level 0 is matrix-free on the SIMP moduli; every coarser level stores its
+// Galerkin operator P^T K P as an assembled 3^N-point block stencil in SoA layout.  The reference
+// keeps a dense 24x24 Ke per coarse element (4.6 KB each) AND a block-CSC matrix per level; the
+// assembled stencil is the same linear operator, so smoothing/apply/restriction results agree to
+// roundoff.  The coarsest level is solved exactly through a dense inverse (cuSOLVER potrf/potri,
+// refreshed once per density update) applied as one GEMV, where the reference calls CHOLMOD.
+#pragma once
+#include "sim.h"
+#include "kernels_vec.cuh"
+#include <functional>
+
+namespace vfem {
+
+struct MGBase {
+    int dim = 0;
+    virtual ~MGBase() {}
+};
+
+template <int N>
+struct MG : MGBase {
+    static constexpr int NPE = 1 << N, KS = N * NPE, NST = ipow3(N);
+    struct Level {
+        Grid<N> g;
+        std::vector<uint8_t> dmask; // host mirror (coarse levels: MG.hh:43-84)
+        DevBuf<uint8_t> d_dmask;
+        DevBuf<Real> d_dval;        // zeros on coarse levels
+        DevBuf<Real> x, b, r;       // work vectors m_x, m_b (MG.hh:755-756) + residual scratch
+        DevBuf<Real> S;             // block stencil, levels >= 1
+    };
+    std::shared_ptr<Sim<N>> sim;
+    std::vector<Level> lv;
+    DevBuf<Real> d_C;               // 2^N coarsened reference stiffness matrices (MG.hh:644-648)
+    DevBuf<Real> d_Ainv;            // dense inverse of the coarsest Dirichlet-reduced operator
+    int coarseDofs = 0;
+    unsigned long long builtVersion = 0;
+    bool symmetricGS = true;                       // MG.hh:758
+    bool buildBlockStiffnessMatrices = true;       // MG.hh:746 (kept for API parity; no effect on results)
+    bool buildFinestBlockStiffnessMatrix = false;  // MG.hh:750
+    cudaStream_t stream = 0;
+
+    // PCG state
+    DevBuf<Real> p_x, p_r, p_d, p_Ad, p_s, p_b;
+    DevBuf<Real> d_scal;            // [0] rMr [1] rMrOld [2] dAd [3] rr [4] bb [5..7] scratch
+    DevBuf<Real> d_partials; DevBuf<unsigned int> d_ticket;
+    Real *h_scal = nullptr;         // pinned mirror of d_scal
+    ReduceWork rw;
+    void *cusolverHandle = nullptr;
+    DevBuf<Real> d_solverWork; DevBuf<int> d_info;
+
+    MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels);
+    ~MG();
+    size_t numLevels() const { return lv.size(); }
+    size_t levelDofs(size_t l) const { return size_t(lv.at(l).g.nn) * N; }
+    void syncMasks();
+
+    // operator hierarchy (MG.hh:415-441)
+    void updateElementStiffnessMatrices(bool force = true);
+    // device-pointer operators
+    template <int MODE> void applyMode(size_t l, const Real *u, const Real *b, Real *out);
+    void applyK(size_t l, const Real *u, Real *out);                                   // MG.hh:353-358
+    void computeResidual(size_t l, const Real *u, const Real *b, Real *r);             // MG.hh:401-413
+    void applyKMasked(size_t l, const Real *u, Real *out);
+    void smoothColoured(size_t l, Real *u, const Real *b, bool forward);               // MG.hh:336-340
+    void restriction(size_t lf, const Real *vf, Real *bc);                             // MG.hh:145-180
+    void interpolate(size_t lf, const Real *xc, Real *xf, bool accumulate);            // MG.hh:115-141
+    void zeroOutDirichlet(size_t l, Real *u);                                          // MG.hh:364-378
+    void enforceDirichlet(size_t l, Real *u, bool zero);                               // MG.hh:386-398
+    void coarseSolve(const Real *b, Real *x);                                          // TPS.hh:834-865
+    // cycles (MG.hh:446-553)
+    void vcycle(size_t l, size_t nu, bool residualSystem);
+    void fullMultigrid(size_t l, size_t nu, bool residualSystem);
+    typedef std::function<void(size_t, const Real * /*device x*/)> SolveCb;
+    void solve(const Real *u, const Real *f, size_t numSteps, size_t nu, bool stiffnessUpdated, bool zeroDirichlet,
+               const SolveCb &cb, bool fmg, Real *out);
+    // MG.hh:679-732.  u, b, out: device pointers.  cb(it, x_dev, r_dev, ||r||).  Returns iterations done.
+    typedef std::function<void(size_t, const Real *, const Real *, Real)> PcgCb;
+    size_t pcg(const Real *u, const Real *b, size_t maxIter, Real tol, const PcgCb &cb, size_t mgIterations, size_t nu,
+               bool fmg, Real *out, Real *finalResidualNorm = nullptr);
+    Real dot(const Real *a, const Real *b, size_t n); // deterministic device dot, synchronous
+};
+
+} // namespace vfem

@@ -1,0 +1,112 @@
+// ndr_b200 — V-cycle, full multigrid and MG-preconditioned CG (included by mg.cu inside namespace vfem).
+
+// vcycle (MG.hh:516-553)
+template <int N>
+void MG<N>::vcycle(size_t l, size_t nu, bool residualSystem) {
+    const size_t coarsest = lv.size() - 1;
+    Level &L = lv[l];
+    if (l == coarsest) { coarseSolve(L.b.p, L.x.p); return; }
+    enforceDirichlet(l, L.x.p, residualSystem);
+    for (size_t i = 0; i < nu; ++i) smoothColoured(l, L.x.p, L.b.p, true);
+    computeResidual(l, L.x.p, L.b.p, L.r.p);
+    restriction(l, L.r.p, lv[l + 1].b.p);
+    lv[l + 1].x.zero(stream);
+    vcycle(l + 1, nu, true);
+    interpolate(l, lv[l + 1].x.p, L.x.p, true);
+    for (size_t i = 0; i < nu; ++i) smoothColoured(l, L.x.p, L.b.p, !symmetricGS);
+}
+
+// fullMultigrid (MG.hh:486-508)
+template <int N>
+void MG<N>::fullMultigrid(size_t l, size_t nu, bool residualSystem) {
+    const size_t coarsest = lv.size() - 1;
+    Level &L = lv[l];
+    if (l == coarsest) { coarseSolve(L.b.p, L.x.p); return; }
+    restriction(l, L.b.p, lv[l + 1].b.p);
+    fullMultigrid(l + 1, nu, residualSystem);
+    interpolate(l, lv[l + 1].x.p, L.x.p, false);
+    vcycle(l, nu, residualSystem);
+}
+
+// solve (MG.hh:446-472).  u may be nullptr (= zero initial guess); out may alias lv[0].x.
+template <int N>
+void MG<N>::solve(const Real *u, const Real *f, size_t numSteps, size_t nu, bool stiffnessUpdated, bool zeroDirichlet,
+                  const SolveCb &cb, bool fmg, Real *out) {
+    const size_t bytes = levelDofs(0) * sizeof(Real);
+    syncMasks();
+    if (!stiffnessUpdated) updateElementStiffnessMatrices(true);
+    if (numSteps == 0) {
+        if (u && out != u) VFEM_CUDA(cudaMemcpyAsync(out, u, bytes, cudaMemcpyDeviceToDevice, stream));
+        if (!u) VFEM_CUDA(cudaMemsetAsync(out, 0, bytes, stream));
+        return;
+    }
+    Level &L0 = lv[0];
+    if (u) { if (u != L0.x.p) VFEM_CUDA(cudaMemcpyAsync(L0.x.p, u, bytes, cudaMemcpyDeviceToDevice, stream)); }
+    else L0.x.zero(stream);
+    if (f != L0.b.p) VFEM_CUDA(cudaMemcpyAsync(L0.b.p, f, bytes, cudaMemcpyDeviceToDevice, stream));
+    size_t first = 0;
+    if (fmg) { fullMultigrid(0, nu, zeroDirichlet); if (cb) cb(0, L0.x.p); first = 1; }
+    for (size_t i = first; i < numSteps; ++i) { vcycle(0, nu, zeroDirichlet); if (cb) cb(i, L0.x.p); }
+    if (out != L0.x.p) VFEM_CUDA(cudaMemcpyAsync(out, L0.x.p, bytes, cudaMemcpyDeviceToDevice, stream));
+}
+
+template <int N>
+Real MG<N>::dot(const Real *a, const Real *b, size_t n) {
+    dotKernel<<<reduceBlocks(n), kRedBlock, 0, stream>>>(a, b, n, rw, d_scal.p + 5);
+    VFEM_CHECK_LAUNCH(); countLaunch();
+    VFEM_CUDA(cudaMemcpyAsync(h_scal + 5, d_scal.p + 5, sizeof(Real), cudaMemcpyDeviceToHost, stream));
+    VFEM_CUDA(cudaStreamSynchronize(stream));
+    return h_scal[5];
+}
+
+// preconditionedConjugateGradient (MG.hh:679-732).  All vectors stay in HBM; per iteration the host
+// reads back one scalar (||r||^2) for the stopping test.  alpha and beta are formed on the device
+// from the fused reductions, so there is no other host round trip.
+template <int N>
+size_t MG<N>::pcg(const Real *u, const Real *b, size_t maxIter, Real tol, const PcgCb &cb, size_t mgIterations, size_t nu,
+                  bool fmg, Real *out, Real *finalResidualNorm) {
+    const size_t n = levelDofs(0), bytes = n * sizeof(Real);
+    const int rb = reduceBlocks(n);
+    syncMasks();
+    Real *x = p_x.p, *r = p_r.p, *d = p_d.p, *Ad = p_Ad.p;
+    Real *sc = d_scal.p;
+    VFEM_CUDA(cudaMemcpyAsync(x, u, bytes, cudaMemcpyDeviceToDevice, stream));
+    if (b != p_b.p) VFEM_CUDA(cudaMemcpyAsync(p_b.p, b, bytes, cudaMemcpyDeviceToDevice, stream));
+    b = p_b.p;
+    enforceDirichlet(0, x, false);
+    updateElementStiffnessMatrices(true); // MG.hh:688-689 (+ updateBlockKs)
+    dotKernel<<<rb, kRedBlock, 0, stream>>>(b, b, n, rw, sc + 4); VFEM_CHECK_LAUNCH(); countLaunch();
+    computeResidual(0, x, b, r);
+    dotKernel<<<rb, kRedBlock, 0, stream>>>(r, r, n, rw, sc + 3); VFEM_CHECK_LAUNCH(); countLaunch();
+    VFEM_CUDA(cudaMemcpyAsync(h_scal + 3, sc + 3, 2 * sizeof(Real), cudaMemcpyDeviceToHost, stream));
+    VFEM_CUDA(cudaStreamSynchronize(stream));
+    const Real bnsq = h_scal[4];
+    Real rr = h_scal[3];
+    size_t i = 0; // the reference leaves `i` uninitialised (MG.hh:710); 0 is the intended value
+    bool first = true;
+    while ((i++ < maxIter) && (rr > tol * tol * bnsq)) {
+        Real *s;
+        if (nu == 0) { // applyPreconditionerInv returns r unchanged (MG.hh:477)
+            if (p_s.n != n) p_s.alloc(n);
+            VFEM_CUDA(cudaMemcpyAsync(p_s.p, r, bytes, cudaMemcpyDeviceToDevice, stream));
+            s = p_s.p;
+        } else {
+            solve(nullptr, r, mgIterations, nu, true, true, nullptr, fmg, lv[0].x.p);
+            s = lv[0].x.p;
+        }
+        copyScalarKernel<<<1, 1, 0, stream>>>(sc + 1, sc + 0); VFEM_CHECK_LAUNCH(); countLaunch();
+        maskDotKernel<N><<<rb, kRedBlock, 0, stream>>>(s, r, maskOf(*this, 0), n, rw, sc + 0); VFEM_CHECK_LAUNCH(); countLaunch();
+        updateDirectionKernel<<<rb, kRedBlock, 0, stream>>>(d, s, n, sc + 0, sc + 1, first ? 1 : 0); VFEM_CHECK_LAUNCH(); countLaunch();
+        first = false;
+        applyKMasked(0, d, Ad);
+        dotKernel<<<rb, kRedBlock, 0, stream>>>(d, Ad, n, rw, sc + 2); VFEM_CHECK_LAUNCH(); countLaunch();
+        updateSolutionKernel<<<rb, kRedBlock, 0, stream>>>(x, r, d, Ad, n, sc + 0, sc + 2, rw, sc + 3); VFEM_CHECK_LAUNCH(); countLaunch();
+        VFEM_CUDA(cudaMemcpyAsync(h_scal + 3, sc + 3, sizeof(Real), cudaMemcpyDeviceToHost, stream));
+        VFEM_CUDA(cudaStreamSynchronize(stream));
+        rr = h_scal[3];
+        if (cb) cb(i, x, r, std::sqrt(rr));
+    }
+    if (out != x) VFEM_CUDA(cudaMemcpyAsync(out, x, bytes, cudaMemcpyDeviceToDevice, stream));
+    if (finalResidualNorm) *finalResidualNorm = std::sqrt(rr);
+    return i - 1;
+}

@@ -1,0 +1,229 @@
+// ndr_b200 — TensorProductSimulator host logic + fine-level launches.
+#include "sim.h"
+#include "kernels.cuh"
+#include "kernels_vec.cuh"
+
+namespace vfem {
+
+unsigned long long g_launchCount = 0;
+
+template <int N>
+Sim<N>::Sim(const Real *bbmin, const Real *bbmax, const size_t *elems) {
+    dim = N;
+    int E[N];
+    for (int d = 0; d < N; ++d) {
+        if (elems[d] == 0 || elems[d] > (1u << 20)) throw std::runtime_error("invalid grid size");
+        E[d] = int(elems[d]); mn[d] = bbmin[d]; mx[d] = bbmax[d];
+    }
+    g = makeGrid<N>(E);
+    for (int d = 0; d < N; ++d) {
+        Real len = mx[d] - mn[d];
+        spacing[d] = len / (Real(g.n[d]) - 1.0); // TPS.hh:275
+        h[d] = len / Real(g.E[d]);               // TPS.hh:287
+    }
+    dmask.assign(g.nn, 0); dval.assign(size_t(g.nn) * N, 0.0);
+    force.assign(size_t(g.nn) * N, 0.0); hasForce.assign(g.nn, 0);
+    d_rho.alloc(g.ne); d_rho.zero(stream); // NDVector value-initialises densities to 0
+    d_Ey.alloc(g.ne);
+    updateK0();
+}
+
+template <int N>
+void Sim<N>::setIsotropic(Real young, Real nu) {
+    lambda = (N == 2) ? (nu * young) / (1.0 - nu * nu)                      // plane stress
+                      : (nu * young) / ((1.0 + nu) * (1.0 - 2.0 * nu));
+    mu = young / (2.0 + 2.0 * nu);
+    updateK0();
+}
+
+// K0[(p,a),(q,b)] = vol * sum_gp w * [ lambda d_a phi_p d_b phi_q + mu d_b phi_p d_a phi_q
+//                                     + mu delta_ab grad phi_p . grad phi_q ]
+// which is eps(phi_p e_a) : C : eps(phi_q e_b) for isotropic C, integrated with the 2-point
+// Gauss rule per axis (TensorProductQuadrature.hh:123-132); gradients scaled by 1/h_d.
+template <int N>
+void Sim<N>::updateK0() {
+    const Real gp[2] = {0.5 - 0.5 / std::sqrt(3.0), 0.5 + 0.5 / std::sqrt(3.0)};
+    Real vol = 1.0;
+    for (int d = 0; d < N; ++d) vol *= h[d];
+    for (int i = 0; i < KS * KS; ++i) K0.k[i] = 0.0;
+    for (int q = 0; q < (1 << N); ++q) { // quadrature point
+        Real xi[N], w = 1.0;
+        for (int d = 0; d < N; ++d) { xi[d] = gp[(q >> (N - 1 - d)) & 1]; w *= 0.5; }
+        Real grad[NPE][N];
+        for (int p = 0; p < NPE; ++p)
+            for (int a = 0; a < N; ++a) {
+                Real v = 1.0;
+                for (int d = 0; d < N; ++d) {
+                    int bit = (p >> (N - 1 - d)) & 1;
+                    if (d == a) v *= (bit ? 1.0 : -1.0) / h[d];
+                    else v *= bit ? xi[d] : 1.0 - xi[d];
+                }
+                grad[p][a] = v;
+            }
+        for (int p = 0; p < NPE; ++p)
+            for (int r = 0; r < NPE; ++r) {
+                Real gg = 0.0;
+                for (int k = 0; k < N; ++k) gg += grad[p][k] * grad[r][k];
+                for (int a = 0; a < N; ++a)
+                    for (int b = 0; b < N; ++b) {
+                        Real v = lambda * grad[p][a] * grad[r][b] + mu * grad[p][b] * grad[r][a] + (a == b ? mu * gg : 0.0);
+                        K0.k[(p * N + a) * KS + r * N + b] += w * vol * v;
+                    }
+            }
+    }
+    // exact symmetry (the reference mirrors the upper triangle, TPS.hh:136-138)
+    for (int i = 0; i < KS; ++i)
+        for (int j = i + 1; j < KS; ++j) K0.k[j * KS + i] = K0.k[i * KS + j];
+    touchStiffness();
+}
+
+template <int N>
+static bool inRegion(const Real *p, const Real *lo, const Real *hi) { // inclusive, Geometry.hh:276-279
+    for (int d = 0; d < N; ++d) if (!(p[d] >= lo[d] && p[d] <= hi[d])) return false;
+    return true;
+}
+
+template <int N>
+void Sim<N>::addForceRegion(const Real *lo, const Real *hi, const Real *value) {
+    std::vector<size_t> hit;
+    Real p[N];
+    for (size_t ni = 0; ni < size_t(g.nn); ++ni) { nodePosition(ni, p); if (inRegion<N>(p, lo, hi)) hit.push_back(ni); }
+    if (hit.empty()) throw std::runtime_error("Force constraint region unmatched");
+    for (size_t ni : hit) {
+        hasForce[ni] = 1;
+        for (int d = 0; d < N; ++d) force[ni * N + d] = value[d] / Real(hit.size()); // overwrite, TPS.hh:385-388
+    }
+}
+
+template <int N>
+void Sim<N>::setDirichlet(size_t ni, const uint8_t *compMask, const Real *value) {
+    for (int c = 0; c < N; ++c) {
+        if (!compMask[c]) continue;
+        if (!((dmask[ni] >> c) & 1)) { dmask[ni] |= uint8_t(1u << c); dval[ni * N + c] = value[c]; }
+        else if (std::abs(dval[ni * N + c] - value[c]) > 1e-10) throw std::runtime_error("Conflicting dirichlet displacements.");
+    }
+    bcDirty = true;
+}
+
+template <int N>
+void Sim<N>::addDirichletRegion(const Real *lo, const Real *hi, const uint8_t *compMask, const Real *value) {
+    size_t cnt = 0; Real p[N];
+    for (size_t ni = 0; ni < size_t(g.nn); ++ni) { nodePosition(ni, p); if (inRegion<N>(p, lo, hi)) { ++cnt; setDirichlet(ni, compMask, value); } }
+    if (cnt == 0) throw std::runtime_error("Dirichlet region unmatched");
+}
+
+template <int N>
+void Sim<N>::buildLoadVectorHost(Real *f) const {
+    const size_t nd = numDofs();
+    for (size_t i = 0; i < nd; ++i) f[i] = 0.0;
+    for (size_t ni = 0; ni < size_t(g.nn); ++ni)
+        if (hasForce[ni]) for (int d = 0; d < N; ++d) f[ni * N + d] += force[ni * N + d];
+}
+
+template <int N>
+void Sim<N>::syncBC() {
+    if (!bcDirty && d_dmask.n == size_t(g.nn)) return;
+    d_dmask.upload(dmask, stream);
+    d_dval.upload(dval, stream);
+    VFEM_CUDA(cudaStreamSynchronize(stream));
+    bcDirty = false;
+}
+
+template <int N>
+void Sim<N>::setDensities(const Real *rho, MemSpace ms) {
+    VFEM_CUDA(cudaMemcpyAsync(d_rho.p, rho, size_t(g.ne) * sizeof(Real), ms == MS_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, stream));
+    if (ms == MS_HOST) VFEM_CUDA(cudaStreamSynchronize(stream));
+    touchStiffness();
+}
+
+template <int N>
+void Sim<N>::setUniformDensities(Real v) {
+    if (v < 0 || v > 1) throw std::runtime_error("Density value must be in [0, 1]"); // TPS.hh:457
+    std::vector<Real> hrho(g.ne, v);
+    setDensities(hrho.data(), MS_HOST);
+}
+
+template <int N>
+void Sim<N>::setElementDensity(size_t ei, Real v) {
+    if (v < 0 || v > 1) throw std::runtime_error("Density value must be in [0, 1]"); // TPS.hh:464
+    if (ei >= size_t(g.ne)) throw std::runtime_error("element index out of range");
+    VFEM_CUDA(cudaMemcpyAsync(d_rho.p + ei, &v, sizeof(Real), cudaMemcpyHostToDevice, stream));
+    VFEM_CUDA(cudaStreamSynchronize(stream));
+    touchStiffness();
+}
+
+template <int N>
+Real Sim<N>::elementDensity(size_t ei) const {
+    if (ei >= size_t(g.ne)) throw std::runtime_error("element index out of range");
+    Real v;
+    VFEM_CUDA(cudaMemcpyAsync(&v, d_rho.p + ei, sizeof(Real), cudaMemcpyDeviceToHost, stream));
+    VFEM_CUDA(cudaStreamSynchronize(stream));
+    return v;
+}
+
+template <int N>
+void Sim<N>::getDensities(Real *out, MemSpace ms) const {
+    VFEM_CUDA(cudaMemcpyAsync(out, d_rho.p, size_t(g.ne) * sizeof(Real), ms == MS_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, stream));
+    VFEM_CUDA(cudaStreamSynchronize(stream));
+}
+
+template <int N>
+const Real *Sim<N>::moduli() {
+    if (EyDirty) {
+        int blocks = reduceBlocks(g.ne);
+        simpKernel<<<blocks, kRedBlock, 0, stream>>>(d_rho.p, d_Ey.p, size_t(g.ne), E0, Emin, gamma);
+        VFEM_CHECK_LAUNCH(); countLaunch();
+        EyDirty = false;
+    }
+    return d_Ey.p;
+}
+
+template <int N>
+void Sim<N>::applyK(const Real *u, Real *out) {
+    const Real *Ey = moduli();
+    applyFineKernel<N, 0><<<(g.nn + kBlock - 1) / kBlock, kBlock, 0, stream>>>(g, K0, Ey, u, nullptr, nullptr, out);
+    VFEM_CHECK_LAUNCH(); countLaunch();
+}
+
+// g_e = -1/2 gamma rho_e^(gamma-1) (E0 - Emin) u_e^T K0 u_e     (TPS.hh:730-751)
+template <int N>
+__global__ void __launch_bounds__(kBlock) complianceGradientKernel(Grid<N> g, K0Param<N> K, const Real *__restrict__ rho,
+                                                                    const Real *__restrict__ u, Real *__restrict__ grad, Real gamma,
+                                                                    Real dE) {
+    constexpr int NPE = 1 << N, KS = N * NPE;
+    int e = blockIdx.x * kBlock + threadIdx.x;
+    if (e >= g.ne) return;
+    int base = 0, r = e;
+#pragma unroll
+    for (int d = N - 1; d > 0; --d) { int q = r / g.E[d]; base += (r - q * g.E[d]) * g.ninc[d]; r = q; }
+    base += r * g.ninc[0];
+    Real ul[KS];
+#pragma unroll
+    for (int m = 0; m < NPE; ++m) {
+        int off = 0;
+#pragma unroll
+        for (int d = 0; d < N; ++d) off += ((m >> (N - 1 - d)) & 1) * g.ninc[d];
+#pragma unroll
+        for (int c = 0; c < N; ++c) ul[m * N + c] = u[size_t(base + off) * N + c];
+    }
+    Real q = 0.0;
+#pragma unroll
+    for (int i = 0; i < KS; ++i) {
+        Real s = 0.0;
+#pragma unroll
+        for (int j = 0; j < KS; ++j) s = fma(K.k[i * KS + j], ul[j], s);
+        q = fma(ul[i], s, q);
+    }
+    grad[e] = -0.5 * gamma * pow(rho[e], gamma - 1.0) * dE * q;
+}
+
+template <int N>
+void Sim<N>::complianceGradient(const Real *u, Real *grad) {
+    complianceGradientKernel<N><<<(g.ne + kBlock - 1) / kBlock, kBlock, 0, stream>>>(g, K0, d_rho.p, u, grad, gamma, E0 - Emin);
+    VFEM_CHECK_LAUNCH(); countLaunch();
+}
+
+template struct Sim<2>;
+template struct Sim<3>;
+
+} // namespace vfem

@@ -1,0 +1,76 @@
+// ndr_b200 — host side of the regular-grid elasticity simulator.
+// Mirrors the public surface of the reference's TensorProductSimulator<1,...> for the solve path
+// (VoxelFEM/TensorProductSimulator.hh:219-1419): grid + indexing, material -> K0, boundary
+// conditions, SIMP moduli, K u, compliance gradient.  All field data lives in HBM.
+#pragma once
+#include "common.h"
+#include <cmath>
+#include <memory>
+
+namespace vfem {
+
+struct SimBase {
+    int dim = 0;
+    cudaStream_t stream = 0;
+    virtual ~SimBase() {}
+};
+
+template <int N>
+struct Sim : SimBase {
+    static constexpr int NPE = 1 << N, KS = N * NPE, NST = ipow3(N);
+
+    Grid<N> g;
+    Real mn[N], mx[N], h[N], spacing[N];
+    Real lambda = 0.0, mu = 0.5;       // default ETensor(1, 0), TPS.hh:1379
+    K0Param<N> K0;                     // reference element stiffness for unit modulus
+    Real E0 = 1.0, Emin = 1e-9, gamma = 3.0; // TPS.hh:1392-1394
+
+    // boundary data (host mirrors; device copies refreshed lazily)
+    std::vector<uint8_t> dmask;        // per node, bit c = component c fixed
+    std::vector<Real> dval;            // nn*N
+    std::vector<Real> force;           // nn*N
+    std::vector<uint8_t> hasForce;     // nn
+    bool bcDirty = true;
+    DevBuf<uint8_t> d_dmask;
+    DevBuf<Real> d_dval;
+
+    // densities and moduli (device is authoritative)
+    DevBuf<Real> d_rho, d_Ey;
+    bool EyDirty = true;
+    unsigned long long densityVersion = 1; // bumped whenever K(rho) changes
+
+    Sim(const Real *bbmin, const Real *bbmax, const size_t *elems);
+
+    // TPS.hh:274-279
+    void nodePosition(size_t ni, Real *p) const {
+        for (int d = N - 1; d >= 0; --d) { size_t i = ni % size_t(g.n[d]); ni /= size_t(g.n[d]); p[d] = mn[d] + Real(i) * spacing[d]; }
+    }
+    size_t numNodes() const { return size_t(g.nn); }
+    size_t numElements() const { return size_t(g.ne); }
+    size_t numDofs() const { return size_t(g.nn) * N; }
+
+    void setIsotropic(Real young, Real nu);   // ElasticityTensor.hh:100-115
+    void updateK0();                          // TPS.hh:127-140,1358-1366
+    void touchStiffness() { EyDirty = true; ++densityVersion; }
+
+    // boundary conditions (TPS.hh:358-409, Node::setDirichlet TPS.hh:49-63)
+    void addForceRegion(const Real *lo, const Real *hi, const Real *value);
+    void addDirichletRegion(const Real *lo, const Real *hi, const uint8_t *compMask, const Real *value);
+    void setDirichlet(size_t ni, const uint8_t *compMask, const Real *value);
+    void buildLoadVectorHost(Real *f) const;  // TPS.hh:893-901
+    void syncBC();
+
+    // densities
+    void setDensities(const Real *rho, MemSpace ms);
+    void setUniformDensities(Real v);         // TPS.hh:456-461
+    void setElementDensity(size_t ei, Real v);// TPS.hh:463-468
+    Real elementDensity(size_t ei) const;
+    void getDensities(Real *out, MemSpace ms) const;
+    const Real *moduli();                     // refreshes E(rho) when stale
+
+    // operators on device pointers
+    void applyK(const Real *u, Real *out);    // TPS.hh:905-952
+    void complianceGradient(const Real *u, Real *g); // TPS.hh:730-751
+};
+
+} // namespace vfem
