@@ -264,6 +264,7 @@ class TensorProductSimulator:
         return g
 
     def multigridSolver(self, numCoarseningLevels):
+        from .voxelfem_mg import MultigridSolver
         return MultigridSolver(self, numCoarseningLevels)
 
     def solve(self, f):
