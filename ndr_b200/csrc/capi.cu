@@ -47,7 +47,9 @@ struct Staged {
     }
     void finish() {
         for (auto &o : outs) VFEM_CUDA(cudaMemcpyAsync(o.first.first, o.first.second, o.second * sizeof(double), cudaMemcpyDeviceToHost, stream));
-        VFEM_CUDA(cudaStreamSynchronize(stream));
+        // device-resident calls stay asynchronous on the library stream (the caller synchronises once, like any
+        // CUDA library); calls with host arrays return only when the results have landed
+        if (!outs.empty() || !temps.empty()) VFEM_CUDA(cudaStreamSynchronize(stream));
         outs.clear();
     }
     ~Staged() { for (double *t : temps) cudaFree(t); }

@@ -251,7 +251,9 @@ class TensorProductSimulator:
                 raise RuntimeError("device-resident applyK needs a preallocated `out` device array")
             check(lib().vfem_tps_apply_k(self._h, a.ptr, _dev_ptr(out, self.numDoFs()), DEVICE))
             return out
-        res = np.empty((self.numNodes(), self.N))
+        res = np.empty((self.numNodes(), self.N)) if out is None else out
+        if res.dtype != np.float64 or not res.flags.c_contiguous or res.size != self.numDoFs():
+            raise RuntimeError("`out` must be a C-contiguous float64 array with numNodes*N entries")
         check(lib().vfem_tps_apply_k(self._h, a.ptr, _ptr(res), HOST))
         return res
 
