@@ -61,6 +61,13 @@ int vfem_tps_set_element_density(vfem_tps_t h, size_t ei, double v);            
 int vfem_tps_element_density(vfem_tps_t h, size_t ei, double *v);                   /* elementDensity */
 int vfem_tps_get_densities(vfem_tps_t h, double *rho, int memspace);                /* getDensities */
 int vfem_tps_apply_k(vfem_tps_t h, const double *u, double *out, int memspace);     /* applyK (TPS.hh:905-952) */
+/* kernel selection for the fine-level apply (no reference counterpart): variant 0 = auto (element-marching
+ * Walsh-Hadamard kernel when K0 has the required symmetry), 1 = per-node gather kernel, 2 = marching kernel
+ * with dense 3x3 blocks (the variant used when K0 lacks the isotropic zero pattern).  info[7] =
+ * {march kernel in use, K0 structure (0 none / 1 dense blocks / 2 isotropic pattern), tile shape id, layers per
+ * chunk, grid x, grid y, grid z} */
+int vfem_tps_set_apply_variant(vfem_tps_t h, int variant);
+int vfem_tps_apply_info(vfem_tps_t h, int *info);
 int vfem_tps_compliance_gradient(vfem_tps_t h, const double *u, double *g, int memspace); /* complianceGradient (TPS.hh:730-751) */
 
 /* ---- MultigridSolver ------------------------------------------------------------------------- */

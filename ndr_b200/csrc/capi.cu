@@ -133,6 +133,10 @@ int vfem_tps_get_densities(vfem_tps_t h, double *rho, int ms) { API_TRY WITH_SIM
 int vfem_tps_apply_k(vfem_tps_t h, const double *u, double *out, int ms) {
     API_TRY WITH_SIM(h, Staged st(s.stream); const double *du = st.in(u, s.numDofs(), ms); double *dout = st.out(out, s.numDofs(), ms);
                      s.applyK(du, dout); st.finish();); API_CATCH }
+int vfem_tps_set_apply_variant(vfem_tps_t h, int variant) { API_TRY WITH_SIM(h, s.applyVariant = variant;); API_CATCH }
+int vfem_tps_apply_info(vfem_tps_t h, int *info) {
+    API_TRY WITH_SIM(h, info[0] = s.useMarch() ? 1 : 0; info[1] = s.khatStructure; info[2] = s.marchPlan.cfg; info[3] = s.marchPlan.XC;
+                     info[4] = int(s.marchPlan.grid.x); info[5] = int(s.marchPlan.grid.y); info[6] = int(s.marchPlan.grid.z);); API_CATCH }
 int vfem_tps_compliance_gradient(vfem_tps_t h, const double *u, double *g, int ms) {
     API_TRY WITH_SIM(h, Staged st(s.stream); const double *du = st.in(u, s.numDofs(), ms); double *dg = st.out(g, s.numElements(), ms);
                      s.complianceGradient(du, dg); st.finish();); API_CATCH }

@@ -186,12 +186,8 @@ template <int MODE>
 void MG<N>::applyMode(size_t l, const Real *u, const Real *b, Real *out) {
     const Level &L = lv.at(l);
     const unsigned blocks = unsigned((L.g.nn + kBlock - 1) / kBlock);
-    if (l == 0) {
-        const Real *Ey = sim->moduli();
-        applyFineKernel<N, MODE><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), out);
-    } else {
-        applyStencilKernel<N, MODE><<<blocks, kBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), out);
-    }
+    if (l == 0) { sim->template applyFine<MODE>(u, b, maskOf(*this, 0), out); return; }
+    applyStencilKernel<N, MODE><<<blocks, kBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), out);
     VFEM_CHECK_LAUNCH(); countLaunch();
 }
 

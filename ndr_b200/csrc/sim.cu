@@ -25,6 +25,11 @@ Sim<N>::Sim(const Real *bbmin, const Real *bbmax, const size_t *elems) {
     force.assign(size_t(g.nn) * N, 0.0); hasForce.assign(g.nn, 0);
     d_rho.alloc(g.ne); d_rho.zero(stream); // NDVector value-initialises densities to 0
     d_Ey.alloc(g.ne);
+    if (N == 3) {
+        int dev = 0, sms = 148;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        marchPlan = planMarch(reinterpret_cast<const Grid<3> &>(g), sms > 0 ? sms : 148);
+    }
     updateK0();
 }
 
@@ -74,6 +79,7 @@ void Sim<N>::updateK0() {
     // exact symmetry (the reference mirrors the upper triangle, TPS.hh:136-138)
     for (int i = 0; i < KS; ++i)
         for (int j = i + 1; j < KS; ++j) K0.k[j * KS + i] = K0.k[i * KS + j];
+    if (N == 3) khatStructure = computeKhat(K0.k, Khat);
     touchStiffness();
 }
 
@@ -179,11 +185,18 @@ const Real *Sim<N>::moduli() {
 }
 
 template <int N>
-void Sim<N>::applyK(const Real *u, Real *out) {
+template <int MODE>
+void Sim<N>::applyFine(const Real *u, const Real *b, const uint8_t *mask, Real *out) {
     const Real *Ey = moduli();
-    applyFineKernel<N, 0><<<(g.nn + kBlock - 1) / kBlock, kBlock, 0, stream>>>(g, K0, Ey, u, nullptr, nullptr, out);
+    if (useMarch())
+        launchApplyMarch<MODE>(reinterpret_cast<const Grid<3> &>(g), Khat, khatStructure == 2 && applyVariant != 2, marchPlan, Ey, u, b, mask, out, stream);
+    else
+        applyFineKernel<N, MODE><<<(g.nn + kBlock - 1) / kBlock, kBlock, 0, stream>>>(g, K0, Ey, u, b, mask, out);
     VFEM_CHECK_LAUNCH(); countLaunch();
 }
+
+template <int N>
+void Sim<N>::applyK(const Real *u, Real *out) { applyFine<0>(u, nullptr, nullptr, out); }
 
 // g_e = -1/2 gamma rho_e^(gamma-1) (E0 - Emin) u_e^T K0 u_e     (TPS.hh:730-751)
 template <int N>
@@ -225,5 +238,8 @@ void Sim<N>::complianceGradient(const Real *u, Real *grad) {
 
 template struct Sim<2>;
 template struct Sim<3>;
+#define VFEM_INST(N, M) template void Sim<N>::applyFine<M>(const Real *, const Real *, const uint8_t *, Real *);
+VFEM_INST(2, 0) VFEM_INST(2, 1) VFEM_INST(2, 2) VFEM_INST(3, 0) VFEM_INST(3, 1) VFEM_INST(3, 2)
+#undef VFEM_INST
 
 } // namespace vfem

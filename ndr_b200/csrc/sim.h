@@ -4,6 +4,7 @@
 // conditions, SIMP moduli, K u, compliance gradient.  All field data lives in HBM.
 #pragma once
 #include "common.h"
+#include "apply_march.cuh"
 #include <cmath>
 #include <memory>
 
@@ -24,6 +25,12 @@ struct Sim : SimBase {
     Real lambda = 0.0, mu = 0.5;       // default ETensor(1, 0), TPS.hh:1379
     K0Param<N> K0;                     // reference element stiffness for unit modulus
     Real E0 = 1.0, Emin = 1e-9, gamma = 3.0; // TPS.hh:1392-1394
+    // 3-D only: Walsh-Hadamard block form of K0 for the marching apply (apply_march.cuh)
+    KhatParam Khat;
+    int khatStructure = 0;             // 0: not block diagonal -> gather kernel; 1: dense blocks; 2: isotropic pattern
+    MarchPlan marchPlan;
+    int applyVariant = 0;              // 0 = auto (marching kernel when K0 allows it), 1 = per-node gather kernel, 2 = marching kernel with dense 3x3 blocks
+    bool useMarch() const { return N == 3 && khatStructure > 0 && applyVariant != 1; }
 
     // boundary data (host mirrors; device copies refreshed lazily)
     std::vector<uint8_t> dmask;        // per node, bit c = component c fixed
@@ -70,6 +77,8 @@ struct Sim : SimBase {
 
     // operators on device pointers
     void applyK(const Real *u, Real *out);    // TPS.hh:905-952
+    // MODE 0: K u; 1: mask(b - K u); 2: mask(K u)   (fine level; MG.hh:401-413, 719-720)
+    template <int MODE> void applyFine(const Real *u, const Real *b, const uint8_t *mask, Real *out);
     void complianceGradient(const Real *u, Real *g); // TPS.hh:730-751
 };
 

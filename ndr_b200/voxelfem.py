@@ -257,6 +257,16 @@ class TensorProductSimulator:
         check(lib().vfem_tps_apply_k(self._h, a.ptr, _ptr(res), HOST))
         return res
 
+    # kernel selection of the fine-level apply (not in the reference): 0 = auto, 1 = per-node gather kernel
+    def setApplyVariant(self, variant):
+        check(lib().vfem_tps_set_apply_variant(self._h, int(variant)))
+
+    def applyInfo(self):
+        info = (C.c_int * 7)()
+        check(lib().vfem_tps_apply_info(self._h, info))
+        keys = ("march", "k0_structure", "tile_shape", "layers_per_chunk", "grid_x", "grid_y", "grid_z")
+        return dict(zip(keys, list(info)))
+
     def complianceGradient(self, u):
         a = _Arg(u, self.numDoFs())
         g = np.empty(self.numElements())
