@@ -91,6 +91,7 @@ applyMarchKernel(Grid<3> g, KhatParam kh, const Real *__restrict__ Ey, const Rea
     const bool edgeLoad = live && !nextInWarp;            // loads node z+1 itself
     const bool xSend = live && !nextInWarp && (tx + 1 < ZT);
     const bool xRecv = live && !prevInWarp && (tx > 0);
+    const bool xRecvBelow = live && ry > 0 && tx > 0 && (((t - ZT) & 31) == 0); // thread (ry-1, tx) is an xRecv thread
     const bool spz = live && (tx == ZT - 1) && (z + 1 == nz - 1);
     const bool spRow = (y0 + RY == ny - 1);               // thread row RY-1 also owns node row ny-1
     const bool ownYZ = (ry > 0 || blockIdx.y == 0) && (tx > 0 || blockIdx.x == 0);
@@ -234,11 +235,12 @@ applyMarchKernel(Grid<3> g, KhatParam kh, const Real *__restrict__ Ey, const Rea
         if (xRecv) { // the part of the previous warp's last column that the shuffle could not deliver
             const int s = tx >> 5;
 #pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                Real a = sX[buf][ry][s][c] + sX[buf][ry][s][3 + c];
-                if (ry > 0) a += sX[buf][ry - 1][s][c] - sX[buf][ry - 1][s][3 + c];
-                res[c] += a;
-            }
+            for (int c = 0; c < 3; ++c) res[c] += sX[buf][ry][s][c] + sX[buf][ry][s][3 + c];
+        }
+        if (xRecvBelow) { // ... and the same omission in what the thread of the row below sent up
+            const int s = tx >> 5;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) res[c] += sX[buf][ry - 1][s][c] - sX[buf][ry - 1][s][3 + c];
         }
         if (storePlane) {
             if (nodeA && ownYZ) marchStore<MODE>(g, x, y, z, res, b, dmask, out);

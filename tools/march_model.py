@@ -67,9 +67,9 @@ def reference_apply(E, K, u, Ey):
     return out
 
 
-def march_apply(E, B, u, Ey, RY=4, WZ=2, XC=3, sparse=True):
+def march_apply(E, B, u, Ey, RY=4, ZT=64, XC=3, sparse=True):
     nx, ny, nz = E[0] + 1, E[1] + 1, E[2] + 1
-    ZT = 32 * WZ
+    NT = -(-RY * ZT // 32) * 32
     out = np.full_like(u, np.nan)
     e_bit = [4, 2, 1]
     def ntiles(ne, t):  # tiles of t columns overlapping by one: 1 + ceil(max(0, ne - t) / (t - 1))
@@ -77,8 +77,10 @@ def march_apply(E, B, u, Ey, RY=4, WZ=2, XC=3, sparse=True):
     ntz, nty, nch = ntiles(E[2], ZT), ntiles(E[1], RY), ntiles(E[0], XC)
     ry = np.arange(RY)[:, None] + np.zeros((1, ZT), int)
     tx = np.arange(ZT)[None, :] + np.zeros((RY, 1), int)
-    lane = tx & 31
-    warp = tx >> 5
+    lane = (ry * ZT + tx) & 31           # rows straddle warps when ZT is not a multiple of 32
+    next_in_warp = (lane < 31) & (tx + 1 < ZT)
+    prev_in_warp = (lane > 0) & (tx > 0)
+    XS = ZT // 32 + 2
 
     def ld(p, yy, zz):
         """predicated node load: zeros outside the grid"""
@@ -87,22 +89,25 @@ def march_apply(E, B, u, Ey, RY=4, WZ=2, XC=3, sparse=True):
         v[ok] = u[p, yy[ok], zz[ok]]
         return v
 
-    def shfl_down(a):  # lane i gets lane i+1 (within each 32-lane group); lane 31 keeps garbage (own value)
-        r = a.copy().reshape(RY, WZ, 32, *a.shape[2:])
-        r[:, :, :31] = r[:, :, 1:]
-        return r.reshape(a.shape)
+    def _flat(a):
+        f = np.full((NT,) + a.shape[2:], 1e300)  # idle threads / garbage
+        f[:RY * ZT] = a.reshape((RY * ZT,) + a.shape[2:])
+        return f.reshape((NT // 32, 32) + a.shape[2:])
+
+    def shfl_down(a):  # lane i gets lane i+1 of its warp; lane 31 keeps its own (garbage for the algorithm)
+        f = _flat(a); r = f.copy(); r[:, :31] = f[:, 1:]
+        return r.reshape((NT,) + a.shape[2:])[:RY * ZT].reshape(a.shape)
 
     def shfl_up(a):
-        r = a.copy().reshape(RY, WZ, 32, *a.shape[2:])
-        r[:, :, 1:] = r[:, :, :31].copy()
-        return r.reshape(a.shape)
+        f = _flat(a); r = f.copy(); r[:, 1:] = f[:, :31]
+        return r.reshape((NT,) + a.shape[2:])[:RY * ZT].reshape(a.shape)
 
     for cz, cy, cx in itertools.product(range(ntz), range(nty), range(nch)):
         z0, y0, x0 = cz * (ZT - 1), cy * (RY - 1), cx * (XC - 1)
         x1 = min(x0 + XC, E[0])
         y, z = y0 + ry, z0 + tx
         col_ok = (y < ny - 1) & (z < nz - 1)
-        last31 = lane == 31
+        last31 = ~next_in_warp
 
         def faces(p):
             a, b = ld(p, y, z), ld(p, y + 1, z)
@@ -142,10 +147,12 @@ def march_apply(E, B, u, Ey, RY=4, WZ=2, XC=3, sparse=True):
             # ---- backward for plane x: z stage (shuffles) ----
             zl = Gtot[:, :, :, 0] + Gtot[:, :, :, 1]  # [my][c] part of node z
             zh = Gtot[:, :, :, 0] - Gtot[:, :, :, 1]  # part of node z+1
-            r = shfl_up(zh); r[lane == 0] = 0.0
-            X = np.zeros((RY + 1, WZ + 1, 2, 3))       # smem: zh of lane 31 of (row, warp) -> [row][warp+1]
-            for w in range(WZ):
-                X[:RY, w + 1] = zh[:, 32 * w + 31]
+            r = shfl_up(zh); r[~prev_in_warp] = 0.0
+            X = np.full((RY, XS, 2, 3), np.nan)        # smem: zh of a thread whose z+1 neighbour is in the next warp
+            x_send = ~next_in_warp & (tx + 1 < ZT)
+            x_recv = ~prev_in_warp & (tx > 0)
+            for a, bq in np.argwhere(x_send):
+                X[a, (bq + 1) >> 5] = zh[a, bq]
             Ye = zl + r
             yl = Ye[:, :, 0] + Ye[:, :, 1]
             yhh = Ye[:, :, 0] - Ye[:, :, 1]
@@ -157,10 +164,11 @@ def march_apply(E, B, u, Ey, RY=4, WZ=2, XC=3, sparse=True):
             Ysp = np.zeros((RY + 1, 3)); Ysp[1:] = sph[:, ZT - 1]
             # ---- barrier ----
             res = yl + Yx[:RY]
-            # cross-warp correction for lane 0 of warps > 0
-            for w in range(1, WZ):
-                Xy, Xm = X[:RY, w], np.concatenate([np.zeros((1, 2, 3)), X[:RY - 1, w]])
-                res[:, 32 * w] += (Xy[:, 0] + Xy[:, 1]) + (Xm[:, 0] - Xm[:, 1])
+            # cross-warp correction: the part the shuffle could not deliver, for this row and for the row below
+            for a, bq in np.argwhere(x_recv):
+                res[a, bq] += X[a, bq >> 5, 0] + X[a, bq >> 5, 1]
+                if a + 1 < RY:
+                    res[a + 1, bq] += X[a, bq >> 5, 0] - X[a, bq >> 5, 1]
             store_plane = (x > x0) or (cx == 0)
             ok = (y < ny) & (z < nz) & ((ry > 0) | (cy == 0)) & ((tx > 0) | (cz == 0))
             # tiles own output nodes up to their last thread row / lane; the next tile re-computes the shared one as ghost
@@ -172,9 +180,9 @@ def march_apply(E, B, u, Ey, RY=4, WZ=2, XC=3, sparse=True):
                 # special row: node row y+1 == ny-1 owned by thread row RY-1
                 if y0 + RY == ny - 1:
                     top = yhh[RY - 1].copy()
-                    for w in range(1, WZ):
-                        Xy = X[RY - 1, w]
-                        top[32 * w] += Xy[0] - Xy[1]
+                    for a, bq in np.argwhere(x_recv):
+                        if a == RY - 1:
+                            top[bq] += X[a, bq >> 5, 0] - X[a, bq >> 5, 1]
                     zz = z[RY - 1]
                     okt = (zz < nz) & ((tx[RY - 1] > 0) | (cz == 0))
                     out[x, ny - 1, zz[okt]] = top[okt]
@@ -187,21 +195,23 @@ def main():
     rng = np.random.default_rng(0)
     lam, mu = 0.3 / (1.3 * 0.4), 1.0 / 2.6
     worst = 0.0
-    for E, h, RY, WZ, XC in (([5, 4, 6], [1 / 4, 1 / 4, 1 / 4], 4, 1, 3), ([4, 7, 40], [1 / 4, 1 / 4, 1 / 8], 3, 1, 4),
-                             ([3, 6, 64], [1.0, 0.5, 0.25], 4, 2, 2), ([6, 9, 70], [1.0, 1.0, 1.0], 4, 2, 3),
-                             ([2, 3, 31], [1.0, 1.0, 1.0], 4, 1, 5), ([7, 8, 32], [1.0, 2.0, 1.0], 3, 1, 3),
-                             ([4, 2, 33], [1.0, 2.0, 1.0], 3, 1, 3), ([3, 3, 63], [1.0, 2.0, 1.0], 4, 2, 9)):
+    for E, h, RY, ZT, XC in (([5, 4, 6], [1 / 4, 1 / 4, 1 / 4], 4, 32, 3), ([4, 7, 40], [1 / 4, 1 / 4, 1 / 8], 3, 32, 4),
+                             ([3, 6, 64], [1.0, 0.5, 0.25], 4, 64, 2), ([6, 9, 70], [1.0, 1.0, 1.0], 4, 64, 3),
+                             ([2, 3, 31], [1.0, 1.0, 1.0], 4, 32, 5), ([7, 8, 32], [1.0, 2.0, 1.0], 3, 32, 3),
+                             ([4, 2, 33], [1.0, 2.0, 1.0], 3, 32, 3), ([3, 3, 63], [1.0, 2.0, 1.0], 4, 64, 9),
+                             ([3, 9, 31], [1.0, 2.0, 1.0], 7, 65, 2), ([3, 16, 70], [1.0, 1.0, 1.0], 5, 33, 3),
+                             ([2, 11, 65], [1.0, 1.0, 1.0], 6, 65, 2), ([2, 30, 40], [1.0, 1.0, 1.0], 15, 33, 4)):
         K = k0_hex(h, lam, mu)
         B, off = khat_blocks(K)
         assert off < 1e-15 * np.abs(K).max(), off
         u = rng.standard_normal((E[0] + 1, E[1] + 1, E[2] + 1, 3))
         Ey = rng.uniform(0.01, 1, E)
         ref = reference_apply(E, K, u, Ey)
-        got = march_apply(E, B, u, Ey, RY, WZ, XC)
+        got = march_apply(E, B, u, Ey, RY, ZT, XC)
         assert not np.isnan(got).any(), ("unwritten outputs", E, np.argwhere(np.isnan(got))[:5])
         err = np.abs(got - ref).max() / np.abs(ref).max()
         worst = max(worst, err)
-        print(E, "RY", RY, "WZ", WZ, "XC", XC, "rel err %.2e" % err)
+        print(E, "RY", RY, "ZT", ZT, "XC", XC, "rel err %.2e" % err)
     assert worst < 1e-13
     print("OK")
 
