@@ -25,6 +25,7 @@
 #include "common.h"
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 namespace vfem {
 
@@ -47,224 +48,261 @@ __host__ __device__ constexpr bool khatEntryNonZero(int g, int c, int c2) {
 template <int RY, int ZT>
 struct MarchCfg {
     static constexpr int NT = ((RY * ZT + 31) / 32) * 32;
+    static constexpr int MINB = (512 / NT) > 0 ? (512 / NT) : 1; // resident CTAs per SM the register budget is sized for
     static constexpr int XS = ZT / 32 + 2; // cross-warp slots per row
 };
 
-// MODE 0: out = K u;  MODE 1: out = mask(b - K u);  MODE 2: out = mask(K u)
+// per-thread role bits (kept in one register; tested with single-bit predicates)
+enum : unsigned {
+    MF_LIVE = 1u, MF_COL = 2u, MF_EDGE = 4u, MF_XSEND = 8u, MF_XRECV = 16u, MF_XRECVB = 32u, MF_SPZ = 64u, MF_STORE = 128u,
+    MF_YSEND = 256u, MF_YRECV = 512u, MF_PREV = 1024u, MF_SPSTORE = 2048u, MF_TOP = 4096u, MF_TOPSTORE = 8192u, MF_DZ = 16384u, MF_CHUNK0 = 32768u
+};
+
+// MODE 0: out = K u;  MODE 1: out = mask(b - K u);  MODE 2: out = mask(K u).   n = flat node index
 template <int MODE>
-__device__ __forceinline__ void marchStore(const Grid<3> &g, int x, int y, int z, const Real *v, const Real *__restrict__ b,
-                                           const uint8_t *__restrict__ dmask, Real *__restrict__ out) {
-    const size_t n = (size_t(x) * g.n[1] + y) * g.n[2] + z;
-    unsigned m = 0;
-    if (MODE != 0) m = dmask[n];
+__device__ __forceinline__ void marchStore(unsigned n, const Real *v, const Real *__restrict__ b, const uint8_t *__restrict__ dmask,
+                                           Real *__restrict__ out) {
+    Real *o = out + size_t(n) * 3;
+    if (MODE == 0) { o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; return; }
+    const unsigned m = dmask[n];
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
         Real r = v[c];
-        if (MODE == 1) r = b[n * 3 + c] - r;
-        if (MODE != 0 && ((m >> c) & 1u)) r = 0.0;
-        out[n * 3 + c] = r;
+        if (MODE == 1) r = b[size_t(n) * 3 + c] - r;
+        if ((m >> c) & 1u) r = 0.0;
+        o[c] = r;
     }
 }
 
+// Face quantities F[my*2+mz][c] of one node plane from the raw values of rows y (a) and y+1 (b):
+// z stage by shuffle (threads whose z+1 neighbour is not lane+1 load that node themselves), then y stage.
+__device__ __forceinline__ void marchFaces(const Real (&pa)[3], const Real (&pb)[3], unsigned flags, const Real *__restrict__ qa,
+                                           const Real *__restrict__ qb, Real (&F)[4][3]) {
+    Real an[3], bn[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { an[c] = __shfl_down_sync(0xffffffffu, pa[c], 1); bn[c] = __shfl_down_sync(0xffffffffu, pb[c], 1); }
+    if (flags & MF_EDGE) { // node z+1 (clamped into the grid) of rows y and y+1
+        const int d = (flags & MF_DZ) ? 3 : 0;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { an[c] = qa[d + c]; bn[c] = qb[d + c]; }
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const Real zs0 = pa[c] + an[c], zd0 = pa[c] - an[c], zs1 = pb[c] + bn[c], zd1 = pb[c] - bn[c];
+        F[0][c] = zs0 + zs1; F[2][c] = zs0 - zs1; F[1][c] = zd0 + zd1; F[3][c] = zd0 - zd1;
+    }
+}
+
+// One element layer: uh = Fold +- Fnew, yh = blocks * uh, Gtot = Gprev + E (yh0 + yh1), Gprev = E (yh0 - yh1).
+template <bool SPARSE>
+__device__ __forceinline__ void marchLayer(const KhatParam &kh, const Real (&Fold)[4][3], const Real (&Fnew)[4][3], Real Ee,
+                                           Real (&Gprev)[4][3], Real (&Gtot)[4][3]) {
+    Real uh[8][3], yh[8][3];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            if (!(SPARSE && k == 0)) uh[k][c] = Fold[k][c] + Fnew[k][c];
+            uh[4 + k][c] = Fold[k][c] - Fnew[k][c];
+        }
+#pragma unroll
+    for (int gi = 0; gi < 8; ++gi)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const int m = gi ^ khatAxisBit(c);
+            bool first = true;
+            Real acc = 0.0;
+#pragma unroll
+            for (int c2 = 0; c2 < 3; ++c2) {
+                if (SPARSE && !khatEntryNonZero(gi, c, c2)) continue;
+                const int m2 = gi ^ khatAxisBit(c2);
+                acc = first ? kh.b[gi][c][c2] * uh[m2][c2] : fma(kh.b[gi][c][c2], uh[m2][c2], acc);
+                first = false;
+            }
+            yh[m][c] = acc;
+        }
+    const Real nEe = -Ee;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            if (SPARSE && k == 0) { // yh[0][c] == 0
+                Gtot[k][c] = fma(Ee, yh[4][c], Gprev[k][c]);
+                Gprev[k][c] = nEe * yh[4][c];
+            } else {
+                Gtot[k][c] = fma(Ee, yh[k][c] + yh[4 + k][c], Gprev[k][c]);
+                Gprev[k][c] = Ee * (yh[k][c] - yh[4 + k][c]);
+            }
+        }
+}
+
 template <int MODE, bool SPARSE, int RY, int ZT>
-__global__ void __launch_bounds__(MarchCfg<RY, ZT>::NT, 1)
+__global__ void __launch_bounds__(MarchCfg<RY, ZT>::NT, MarchCfg<RY, ZT>::MINB)
 applyMarchKernel(Grid<3> g, KhatParam kh, const Real *__restrict__ Ey, const Real *__restrict__ u, const Real *__restrict__ b,
                  const uint8_t *__restrict__ dmask, Real *__restrict__ out, int XC) {
     constexpr int XS = MarchCfg<RY, ZT>::XS;
     __shared__ Real sYx[2][RY][3][ZT];   // row ry -> slot ry+1 : y-stage part for node row y+1
-    __shared__ Real sX[2][RY][XS][6];    // zh of a lane-31 thread for the lane-0 thread of the next warp
+    __shared__ Real sX[2][RY][XS][6];    // zh of a thread whose z+1 neighbour sits in the next warp
     __shared__ Real sYsp[2][RY][3];      // y exchange of the special last-z node column
 
-    const int t = threadIdx.x;
-    const int ry = t / ZT, tx = t - ry * ZT, lane = t & 31;
-    const bool live = ry < RY;
-    const int nx = g.n[0], ny = g.n[1], nz = g.n[2];
-    const int Ex = g.E[0];
-    const int z0 = blockIdx.x * (ZT - 1), y0 = blockIdx.y * (RY - 1), x0 = blockIdx.z * (XC - 1);
+    const int nx = g.n[0], ny = g.n[1], nz = g.n[2], Ex = g.E[0];
+    const int x0 = blockIdx.z * (XC - 1);
     const int x1 = min(x0 + XC, Ex);
-    const int y = y0 + ry, z = z0 + tx;
-    const bool nodeA = live && y < ny && z < nz;          // (y, z)
-    const bool nodeB = live && y + 1 < ny && z < nz;      // (y+1, z)
-    const bool colOk = live && y < ny - 1 && z < nz - 1;
-    const bool nextInWarp = (lane < 31) && (tx + 1 < ZT); // z+1 neighbour is lane+1 of this warp
-    const bool prevInWarp = (lane > 0) && (tx > 0);
-    const bool edgeLoad = live && !nextInWarp;            // loads node z+1 itself
-    const bool xSend = live && !nextInWarp && (tx + 1 < ZT);
-    const bool xRecv = live && !prevInWarp && (tx > 0);
-    const bool xRecvBelow = live && ry > 0 && tx > 0 && (((t - ZT) & 31) == 0); // thread (ry-1, tx) is an xRecv thread
-    const bool spz = live && (tx == ZT - 1) && (z + 1 == nz - 1);
-    const bool spRow = (y0 + RY == ny - 1);               // thread row RY-1 also owns node row ny-1
-    const bool ownYZ = (ry > 0 || blockIdx.y == 0) && (tx > 0 || blockIdx.x == 0);
-    const size_t planeStride = size_t(ny) * nz * 3;
-    const Real *uA = u + (size_t(y) * nz + z) * 3;        // + p * planeStride
-    const Real *eP = Ey + size_t(y) * g.E[2] + z;         // + x * E1*E2
-    const size_t eStride = size_t(g.E[1]) * g.E[2];
+    unsigned flags, offA, offB, eOff, nodeBase, sIdx; // sIdx = ry * 3 * ZT + tx : element index into sYx[buf]
+    {
+        const int t = threadIdx.x, lane = t & 31;
+        int ry = t / ZT;
+        const int tx = t - ry * ZT;
+        const bool live = ry < RY;
+        if (!live) ry = RY - 1;
+        const int z0 = blockIdx.x * (ZT - 1), y0 = blockIdx.y * (RY - 1);
+        const int y = y0 + ry, z = z0 + tx;
+        const bool nextInWarp = (lane < 31) && (tx + 1 < ZT); // z+1 neighbour is lane+1 of this warp
+        const bool prevInWarp = (lane > 0) && (tx > 0);
+        const bool spz = live && (tx == ZT - 1) && (z + 1 == nz - 1);
+        const bool top = live && (y0 + RY == ny - 1) && (ry == RY - 1); // this thread row also owns node row ny-1
+        const bool ownY = (ry > 0 || blockIdx.y == 0), ownZ = (tx > 0 || blockIdx.x == 0);
+        flags = (live ? MF_LIVE : 0u) | ((live && y < ny - 1 && z < nz - 1) ? MF_COL : 0u) | ((live && !nextInWarp) ? MF_EDGE : 0u) |
+                ((live && !nextInWarp && tx + 1 < ZT) ? MF_XSEND : 0u) | ((live && !prevInWarp && tx > 0) ? MF_XRECV : 0u) |
+                ((live && ry > 0 && tx > 0 && (((t - ZT) & 31) == 0)) ? MF_XRECVB : 0u) | (spz ? MF_SPZ : 0u) |
+                ((live && y < ny && z < nz && ownY && ownZ) ? MF_STORE : 0u) | ((live && ry + 1 < RY) ? MF_YSEND : 0u) |
+                ((live && ry > 0) ? MF_YRECV : 0u) | (prevInWarp ? MF_PREV : 0u) | ((spz && y < ny && ownY) ? MF_SPSTORE : 0u) |
+                (top ? MF_TOP : 0u) | ((top && z < nz && ownZ) ? MF_TOPSTORE : 0u) | ((z + 1 < nz) ? MF_DZ : 0u) |
+                (blockIdx.z == 0 ? MF_CHUNK0 : 0u);
+        // addresses are clamped into the grid instead of predicating the loads: an out-of-grid node only ever
+        // feeds element columns whose modulus is forced to 0 (MF_COL clear), so its (finite) value is irrelevant
+        const int yc = min(y, ny - 1), yb = min(y + 1, ny - 1), zc = min(z, nz - 1);
+        offA = unsigned(yc * nz + zc) * 3u; offB = unsigned(yb * nz + zc) * 3u;
+        eOff = unsigned(min(y, g.E[1] - 1) * g.E[2] + min(z, g.E[2] - 1));
+        nodeBase = unsigned(yc * nz + zc);
+        sIdx = unsigned(ry * 3 * ZT + tx);
+    }
+    const Real prevMask = (flags & MF_PREV) ? 1.0 : 0.0;
+    const unsigned planeStride = unsigned(ny) * unsigned(nz) * 3u, planeNodes = unsigned(ny) * unsigned(nz);
+    const unsigned eStride = unsigned(g.E[1]) * unsigned(g.E[2]);
 
-    // raw node values of the plane being prefetched
-    Real pa[3], pb[3];
-    auto loadRaw = [&](int p) {
-        const Real *q = uA + size_t(p) * planeStride;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) { pa[c] = nodeA ? q[c] : 0.0; pb[c] = nodeB ? q[size_t(nz) * 3 + c] : 0.0; }
-    };
-    // face quantities of plane p from the raw values: F[my*2+mz][c]
-    auto faces = [&](int p, Real (&F)[4][3]) {
-        Real an[3], bn[3];
-#pragma unroll
-        for (int c = 0; c < 3; ++c) { an[c] = __shfl_down_sync(0xffffffffu, pa[c], 1); bn[c] = __shfl_down_sync(0xffffffffu, pb[c], 1); }
-        if (edgeLoad) {
-            const Real *q = uA + size_t(p) * planeStride + 3;
-            const bool okA = y < ny && z + 1 < nz, okB = y + 1 < ny && z + 1 < nz;
-#pragma unroll
-            for (int c = 0; c < 3; ++c) { an[c] = okA ? q[c] : 0.0; bn[c] = okB ? q[size_t(nz) * 3 + c] : 0.0; }
-        }
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            const Real zs0 = pa[c] + an[c], zd0 = pa[c] - an[c], zs1 = pb[c] + bn[c], zd1 = pb[c] - bn[c];
-            F[0][c] = zs0 + zs1; F[2][c] = zs0 - zs1; F[1][c] = zd0 + zd1; F[3][c] = zd0 - zd1;
-        }
-    };
-
-    Real Fprev[4][3], Gprev[4][3];
+    Real pa[3], pb[3], FA[4][3], FB[4][3], Gprev[4][3], Enext;
 #pragma unroll
     for (int k = 0; k < 4; ++k)
 #pragma unroll
         for (int c = 0; c < 3; ++c) Gprev[k][c] = 0.0;
-    loadRaw(x0);
-    faces(x0, Fprev);
-    if (x0 + 1 < nx) loadRaw(x0 + 1);
-    Real Enext = (colOk && x0 < Ex) ? eP[size_t(x0) * eStride] : 0.0;
+    {
+        const Real *up = u + size_t(x0) * planeStride;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { pa[c] = up[offA + c]; pb[c] = up[offB + c]; }
+        marchFaces(pa, pb, flags, up + offA, up + offB, FA);
+        up += planeStride; // x0 + 1 <= Ex is always a valid plane
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { pa[c] = up[offA + c]; pb[c] = up[offB + c]; }
+        Enext = Ey[size_t(x0) * eStride + eOff];
+    }
 
-    const int nIter = (x1 - x0) + (x1 == Ex ? 1 : 0);
-    for (int it = 0; it < nIter; ++it) {
+    auto step = [&](const int it, Real (&Fold)[4][3], Real (&Fnew)[4][3]) {
         const int x = x0 + it, buf = it & 1;
         Real Gtot[4][3];
         if (x < Ex) {
-            Real Fnew[4][3];
-            faces(x + 1, Fnew);
-            const Real Ee = Enext;
-            // prefetch the next step's inputs before the arithmetic of this one
-            if (x + 2 < nx && it + 1 < nIter) loadRaw(x + 2);
-            Enext = (colOk && x + 1 < Ex) ? eP[size_t(x + 1) * eStride] : 0.0;
-            // x stage: uh[mx*4 + k][c]
-            Real uh[8][3], yh[8][3];
+            const Real *up1 = u + size_t(x + 1) * planeStride;
+            marchFaces(pa, pb, flags, up1 + offA, up1 + offB, Fnew);
+            const Real Ee = (flags & MF_COL) ? Enext : 0.0;
+            if (x + 2 < nx) { // prefetch the next step's inputs before the arithmetic of this one
+                const Real *up2 = up1 + planeStride;
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-#pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                    if (!(SPARSE && k == 0)) uh[k][c] = Fprev[k][c] + Fnew[k][c];
-                    uh[4 + k][c] = Fprev[k][c] - Fnew[k][c];
-                    Fprev[k][c] = Fnew[k][c];
-                }
-            // 3x3 blocks
-#pragma unroll
-            for (int gi = 0; gi < 8; ++gi)
-#pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                    const int m = gi ^ khatAxisBit(c);
-                    bool first = true;
-                    Real acc = 0.0;
-#pragma unroll
-                    for (int c2 = 0; c2 < 3; ++c2) {
-                        if (SPARSE && !khatEntryNonZero(gi, c, c2)) continue;
-                        const int m2 = gi ^ khatAxisBit(c2);
-                        acc = first ? kh.b[gi][c][c2] * uh[m2][c2] : fma(kh.b[gi][c][c2], uh[m2][c2], acc);
-                        first = false;
-                    }
-                    yh[m][c] = acc;
-                }
-            // inverse x stage + modulus: plane x gets Gprev + E (yh0 + yh1); plane x+1 gets E (yh0 - yh1)
-            const Real nEe = -Ee;
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-#pragma unroll
-                for (int c = 0; c < 3; ++c) {
-                    if (SPARSE && k == 0) { // yh[0][c] == 0
-                        Gtot[k][c] = fma(Ee, yh[4][c], Gprev[k][c]);
-                        Gprev[k][c] = nEe * yh[4][c];
-                    } else {
-                        Gtot[k][c] = fma(Ee, yh[k][c] + yh[4 + k][c], Gprev[k][c]);
-                        Gprev[k][c] = Ee * (yh[k][c] - yh[4 + k][c]);
-                    }
-                }
+                for (int c = 0; c < 3; ++c) { pa[c] = up2[offA + c]; pb[c] = up2[offB + c]; }
+                if (x + 1 < Ex) Enext = Ey[size_t(x + 1) * eStride + eOff];
+            }
+            marchLayer<SPARSE>(kh, Fold, Fnew, Ee, Gprev, Gtot);
         } else {
 #pragma unroll
             for (int k = 0; k < 4; ++k)
 #pragma unroll
                 for (int c = 0; c < 3; ++c) Gtot[k][c] = Gprev[k][c];
         }
-        // ---- backward, plane x.  z stage: index k = my*2 + mz ----
-        Real zl[2][3], zh[2][3], Ye[2][3];
+        // ---- backward, plane x.  z stage (index k = my*2 + mz), then y stage ----
+        Real zh[2][3], Ye[2][3];
 #pragma unroll
         for (int my = 0; my < 2; ++my)
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
-                zl[my][c] = Gtot[my * 2][c] + Gtot[my * 2 + 1][c];
+                const Real zl = Gtot[my * 2][c] + Gtot[my * 2 + 1][c];
                 zh[my][c] = Gtot[my * 2][c] - Gtot[my * 2 + 1][c];
-                Real r = __shfl_up_sync(0xffffffffu, zh[my][c], 1);
-                if (!prevInWarp) r = 0.0;
-                Ye[my][c] = zl[my][c] + r;
+                const Real r = __shfl_up_sync(0xffffffffu, zh[my][c], 1);
+                Ye[my][c] = fma(r, prevMask, zl); // prevMask = 0 where lane-1 is not the z-1 neighbour (r is then this lane's own, finite, value)
             }
-        if (xSend) {
+        Real *sYb = &sYx[buf][0][0][0] + sIdx;
+        Real *sXb = &sX[buf][0][0][0];
+        if (flags & MF_XSEND) {
+            const int ry = sIdx / (3 * ZT), tx = sIdx - ry * 3 * ZT;
 #pragma unroll
             for (int my = 0; my < 2; ++my)
 #pragma unroll
-                for (int c = 0; c < 3; ++c) sX[buf][ry][(tx + 1) >> 5][my * 3 + c] = zh[my][c];
+                for (int c = 0; c < 3; ++c) sXb[(ry * XS + ((tx + 1) >> 5)) * 6 + my * 3 + c] = zh[my][c];
         }
-        Real yl[3], yhh[3];
+        Real res[3], yhh[3];
 #pragma unroll
-        for (int c = 0; c < 3; ++c) { yl[c] = Ye[0][c] + Ye[1][c]; yhh[c] = Ye[0][c] - Ye[1][c]; }
-        if (live && ry + 1 < RY) {
+        for (int c = 0; c < 3; ++c) { res[c] = Ye[0][c] + Ye[1][c]; yhh[c] = Ye[0][c] - Ye[1][c]; }
+        if (flags & MF_YSEND) {
 #pragma unroll
-            for (int c = 0; c < 3; ++c) sYx[buf][ry + 1][c][tx] = yhh[c];
+            for (int c = 0; c < 3; ++c) sYb[(3 + c) * ZT] = yhh[c];
         }
-        Real spl[3], sph[3];
-        if (spz) {
+        if ((flags & (MF_SPZ | MF_YSEND)) == (MF_SPZ | MF_YSEND)) {
 #pragma unroll
-            for (int c = 0; c < 3; ++c) { spl[c] = zh[0][c] + zh[1][c]; sph[c] = zh[0][c] - zh[1][c]; }
-            if (ry + 1 < RY) {
-#pragma unroll
-                for (int c = 0; c < 3; ++c) sYsp[buf][ry + 1][c] = sph[c];
-            }
+            for (int c = 0; c < 3; ++c) sYsp[buf][sIdx / (3 * ZT) + 1][c] = zh[0][c] - zh[1][c];
         }
+#ifndef VFEM_MARCH_NOBAR
         __syncthreads();
-        const bool storePlane = (it > 0) || (blockIdx.z == 0);
-        Real res[3];
+#endif
+        if (flags & MF_YRECV) {
 #pragma unroll
-        for (int c = 0; c < 3; ++c) res[c] = yl[c] + ((live && ry > 0) ? sYx[buf][ry][c][tx] : 0.0);
-        if (xRecv) { // the part of the previous warp's last column that the shuffle could not deliver
-            const int s = tx >> 5;
-#pragma unroll
-            for (int c = 0; c < 3; ++c) res[c] += sX[buf][ry][s][c] + sX[buf][ry][s][3 + c];
+            for (int c = 0; c < 3; ++c) res[c] += sYb[c * ZT];
         }
-        if (xRecvBelow) { // ... and the same omission in what the thread of the row below sent up
-            const int s = tx >> 5;
-#pragma unroll
-            for (int c = 0; c < 3; ++c) res[c] += sX[buf][ry - 1][s][c] - sX[buf][ry - 1][s][3 + c];
+        const Real *sXr = sXb; // -> sX[buf][ry][tx >> 5][0], only formed on the rare paths
+        if (flags & (MF_XRECV | MF_XRECVB)) {
+            const int ry = sIdx / (3 * ZT), tx = sIdx - ry * 3 * ZT;
+            sXr = sXb + (ry * XS + (tx >> 5)) * 6;
         }
-        if (storePlane) {
-            if (nodeA && ownYZ) marchStore<MODE>(g, x, y, z, res, b, dmask, out);
-            if (spz && y < ny && (ry > 0 || blockIdx.y == 0)) {
-                Real v[3];
+        if (flags & MF_XRECV) { // the part of the previous warp's last column that the shuffle could not deliver
 #pragma unroll
-                for (int c = 0; c < 3; ++c) v[c] = spl[c] + (ry > 0 ? sYsp[buf][ry][c] : 0.0);
-                marchStore<MODE>(g, x, y, z + 1, v, b, dmask, out);
-            }
-            if (spRow && live && ry == RY - 1) { // node row ny-1 = y+1: only this element row touches it
-                if (z < nz && (tx > 0 || blockIdx.x == 0)) {
+            for (int c = 0; c < 3; ++c) res[c] += sXr[c] + sXr[3 + c];
+        }
+        if (flags & MF_XRECVB) { // ... and the same omission in what the thread of the row below sent up
+#pragma unroll
+            for (int c = 0; c < 3; ++c) res[c] += sXr[c - XS * 6] - sXr[3 + c - XS * 6];
+        }
+        if (it > 0 || (flags & MF_CHUNK0)) {
+            const unsigned n = unsigned(x) * planeNodes + nodeBase;
+            if (flags & MF_STORE) marchStore<MODE>(n, res, b, dmask, out);
+            if (flags & (MF_SPSTORE | MF_TOP)) { // rare paths: last node column / last node row of the grid
+                if (flags & MF_SPSTORE) {
+                    Real v[3];
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) v[c] = zh[0][c] + zh[1][c] + ((flags & MF_YRECV) ? sYsp[buf][sIdx / (3 * ZT)][c] : 0.0);
+                    marchStore<MODE>(n + 1, v, b, dmask, out);
+                }
+                if (flags & MF_TOPSTORE) {
                     Real v[3];
 #pragma unroll
                     for (int c = 0; c < 3; ++c) v[c] = yhh[c];
-                    if (xRecv) {
-                        const int s = tx >> 5;
+                    if (flags & MF_XRECV) {
 #pragma unroll
-                        for (int c = 0; c < 3; ++c) v[c] += sX[buf][ry][s][c] - sX[buf][ry][s][3 + c];
+                        for (int c = 0; c < 3; ++c) v[c] += sXr[c] - sXr[3 + c];
                     }
-                    marchStore<MODE>(g, x, y + 1, z, v, b, dmask, out);
+                    marchStore<MODE>(n + nz, v, b, dmask, out);
                 }
-                if (spz) marchStore<MODE>(g, x, y + 1, z + 1, sph, b, dmask, out);
+                if ((flags & (MF_TOP | MF_SPZ)) == (MF_TOP | MF_SPZ)) {
+                    Real v[3];
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) v[c] = zh[0][c] - zh[1][c];
+                    marchStore<MODE>(n + nz + 1, v, b, dmask, out);
+                }
             }
         }
+    };
+
+    const int nIter = (x1 - x0) + (x1 == Ex ? 1 : 0);
+    for (int it = 0; it < nIter; it += 2) { // two steps per trip so the face registers ping-pong without copies
+        step(it, FA, FB);
+        if (it + 1 >= nIter) break;
+        step(it + 1, FB, FA);
     }
 }
 
@@ -316,18 +354,23 @@ struct MarchPlan { int cfg = 0, XC = 2; dim3 grid; };
 
 // picks the tile shape with the fewest thread-steps, then the chunk length that fills the SMs (1 CTA / SM)
 inline MarchPlan planMarch(const Grid<3> &g, int numSMs) {
-    static const int shapes[4][2] = {{8, 64}, {16, 32}, {15, 33}, {7, 65}};
+    static const int shapes[7][2] = {{8, 64}, {16, 32}, {15, 33}, {7, 65}, {6, 64}, {4, 64}, {8, 32}};
     MarchPlan best; double bestCost = 1e300;
-    for (int s = 0; s < 4; ++s) {
-        const int RY = shapes[s][0], ZT = shapes[s][1], NT = ((RY * ZT + 31) / 32) * 32;
+    const char *fs = getenv("VFEM_MARCH_SHAPE"), *fx = getenv("VFEM_MARCH_XC"); // experiment overrides
+    for (int s = 0; s < 7; ++s) {
+        if (fs) s = atoi(fs);
+        const int RY = shapes[s][0], ZT = shapes[s][1], NT = ((RY * ZT + 31) / 32) * 32, MINB = 512 / NT > 0 ? 512 / NT : 1;
         const int ty = marchTiles(g.E[1], RY), tz = marchTiles(g.E[2], ZT);
         for (int XC = 2; XC <= (g.E[0] > 2 ? g.E[0] : 2); ++XC) {
+            if (fx) XC = std::max(2, atoi(fx));
             const int nch = marchTiles(g.E[0], XC);
             const long long ctas = (long long)ty * tz * nch;
-            const long long waves = (ctas + numSMs - 1) / numSMs;
-            const double cost = double(waves) * (std::min(XC, g.E[0]) + 2.5) * NT;
+            const long long waves = (ctas + (long long)numSMs * MINB - 1) / ((long long)numSMs * MINB);
+            const double cost = double(waves) * (std::min(XC, g.E[0]) + 2.5) * NT * MINB;
             if (cost < bestCost) { bestCost = cost; best.cfg = s; best.XC = XC; best.grid = dim3(tz, ty, nch); }
+            if (fx) break;
         }
+        if (fs) break;
     }
     return best;
 }
@@ -345,6 +388,9 @@ inline void launchApplyMarch(const Grid<3> &g, const KhatParam &kh, bool sparse,
         VFEM_MARCH_CASE(1, 16, 32)
         VFEM_MARCH_CASE(2, 15, 33)
         VFEM_MARCH_CASE(3, 7, 65)
+        VFEM_MARCH_CASE(4, 6, 64)
+        VFEM_MARCH_CASE(5, 4, 64)
+        VFEM_MARCH_CASE(6, 8, 32)
     }
 #undef VFEM_MARCH_CASE
 }

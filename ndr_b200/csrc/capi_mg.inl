@@ -50,7 +50,10 @@ int vfem_mg_interpolate(vfem_mg_t h, size_t lf, const double *xc, double *xf, in
                     mg.interpolate(lf, dc, df, accumulate != 0); st.finish();); API_CATCH }
 int vfem_mg_level_stencil(vfem_mg_t h, size_t l, double *out) {
     API_TRY WITH_MG(h, if (l == 0 || l >= mg.lv.size()) throw std::runtime_error("level has no assembled operator");
-                    MG_READY(l); mg.lv[l].S.download(out, mg.stream);); API_CATCH }
+                    MG_READY(l);
+                    { std::vector<double> h = mg.lv[l].S.toHost(mg.stream); const int nn = mg.lv[l].g.nn; constexpr int NST = ipow3(N);
+                      for (int n = 0; n < nn; ++n) for (int k = 0; k < NST; ++k) for (int i = 0; i < N * N; ++i)
+                          out[size_t(k * N * N + i) * nn + n] = h[stencilIndex<N>(n, k, i)]; }); API_CATCH }
 int vfem_mg_debug_get(vfem_mg_t h, size_t l, double *x, double *b) {
     API_TRY WITH_MG(h, if (x) mg.lv.at(l).x.download(x, mg.stream); if (b) mg.lv.at(l).b.download(b, mg.stream);); API_CATCH }
 

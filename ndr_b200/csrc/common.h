@@ -96,6 +96,10 @@ struct K0Param {
 
 constexpr int ipow3(int n) { return n == 0 ? 1 : 3 * ipow3(n - 1); }
 
+// assembled coarse-level operator, node-major: entry (a,b) (i = a*N+b) of the block coupling node n to neighbour slot k
+template <int N>
+__host__ __device__ __forceinline__ size_t stencilIndex(int n, int k, int i) { return (size_t(n) * ipow3(N) + k) * (N * N) + i; }
+
 enum MemSpace { MS_HOST = 0, MS_DEVICE = 1 };
 
 // Count of kernels launched by this library (bench.py's "gpu_launches").

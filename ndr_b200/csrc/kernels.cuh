@@ -106,7 +106,9 @@ __device__ __forceinline__ void fineNodeRow(const Grid<N> &g, const K0Param<N> &
 }
 
 // ---- coarse levels: assembled 3^N-point block stencil ---------------------------------------------
-// S[(k*N*N + a*N + b) * nn + n] = K_l[(n,a), (n + delta(k), b)] (zero for out-of-grid neighbours).
+// Node-major: S[(n*3^N + k)*N*N + a*N + b] = K_l[(n,a), (n + delta(k), b)] (zero for out-of-grid neighbours),
+// so the 3^N * N * N coefficients of one node are contiguous and a warp reads them fully coalesced.
+
 // The reference stores the same operator as a block-CSC matrix (TPS.hh:649-720) and applies it
 // with applyTransposeParallel (SparseMatrices.hh:1519-1568).
 template <int N, bool WITH_M>
@@ -129,11 +131,44 @@ __device__ __forceinline__ void stencilNodeRow(const Grid<N> &g, const Real *__r
         for (int a = 0; a < N; ++a)
 #pragma unroll
             for (int b = 0; b < N; ++b) {
-                Real s = S[size_t(k * N * N + a * N + b) * g.nn + n];
+                Real s = S[stencilIndex<N>(n, k, a * N + b)];
                 acc[a] = fma(s, um[b], acc[a]);
                 if (WITH_M && k == NST / 2) M[a * N + b] = s;
             }
     }
+}
+
+// Warp-per-node row of the assembled operator: the node's 3^N*N*N coefficients are read coalesced (lane l takes
+// entries l, l+32, ...), each multiplied with the neighbour value it belongs to, and the N partial row sums are
+// combined with a fixed shuffle tree (deterministic).  All lanes return the full row sums.
+template <int N>
+__device__ __forceinline__ void stencilWarpRow(const Grid<N> &g, const Real *__restrict__ S, const Real *__restrict__ u, const int *idx,
+                                               int n, int lane, Real *acc) {
+    constexpr int NST = ipow3(N), NN = N * N, TOT = NST * NN;
+    const Real *Sn = S + size_t(n) * TOT;
+#pragma unroll
+    for (int a = 0; a < N; ++a) acc[a] = 0.0;
+#pragma unroll
+    for (int j = 0; j < (TOT + 31) / 32; ++j) {
+        const int e = lane + 32 * j;
+        if (e < TOT) {
+            const int k = e / NN, ab = e - k * NN, a = ab / N, b = ab - a * N;
+            int t = k, off = 0; bool ok = true;
+#pragma unroll
+            for (int d = N - 1; d >= 0; --d) {
+                int dl = t % 3 - 1; t /= 3;
+                int v = idx[d] + dl; ok = ok && (v >= 0) && (v < g.n[d]);
+                off += dl * g.ninc[d];
+            }
+            const Real p = ok ? Sn[e] * u[size_t(n + off) * N + b] : 0.0;
+#pragma unroll
+            for (int a2 = 0; a2 < N; ++a2) acc[a2] += (a2 == a) ? p : 0.0;
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < N; ++a)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc[a] += __shfl_xor_sync(0xffffffffu, acc[a], o);
 }
 
 // Gauss-Seidel update of one node (MG.hh:248-264): t = b_n - (K u)_n, then one component-wise
@@ -237,6 +272,51 @@ __global__ void __launch_bounds__(kBlock) gsStencilKernel(Grid<N> g, const Real 
 #pragma unroll
     for (int c = 0; c < N; ++c) tt[c] = b[size_t(n) * N + c] - acc[c];
     gsNodeUpdate<N>(tt, M, dmask[n], forward != 0, u, n);
+}
+
+
+// ---- warp-per-node variants for the assembled levels (small grids: latency- and launch-bound with one thread/node)
+constexpr int kWarpBlock = 256; // 8 nodes per block
+
+template <int N, int MODE>
+__global__ void __launch_bounds__(kWarpBlock) applyStencilWarpKernel(Grid<N> g, const Real *__restrict__ S, const Real *__restrict__ u,
+                                                                      const Real *__restrict__ b, const uint8_t *__restrict__ dmask,
+                                                                      Real *__restrict__ out) {
+    const int n = (blockIdx.x * kWarpBlock + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (n >= g.nn) return;
+    int idx[N]; unflattenNode<N>(g, n, idx);
+    Real acc[N];
+    stencilWarpRow<N>(g, S, u, idx, n, lane, acc);
+    if (lane < N) {
+        const unsigned m = (MODE != 0) ? dmask[n] : 0u;
+        Real v = acc[0];
+#pragma unroll
+        for (int c = 1; c < N; ++c) if (lane == c) v = acc[c];
+        if (MODE == 1) v = b[size_t(n) * N + lane] - v;
+        if ((m >> lane) & 1u) v = 0.0;
+        out[size_t(n) * N + lane] = v;
+    }
+}
+
+template <int N>
+__global__ void __launch_bounds__(kWarpBlock) gsStencilWarpKernel(Grid<N> g, const Real *__restrict__ S, Real *__restrict__ u,
+                                                                   const Real *__restrict__ b, const uint8_t *__restrict__ dmask, int colour,
+                                                                   int forward) {
+    constexpr int NST = ipow3(N), NN = N * N;
+    const int t = (blockIdx.x * kWarpBlock + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    int idx[N];
+    if (!colourNode<N>(g, t, colour, idx)) return;
+    const int n = flattenNode<N>(g, idx);
+    Real acc[N];
+    stencilWarpRow<N>(g, S, u, idx, n, lane, acc);
+    if (lane == 0) {
+        Real M[NN], tt[N];
+#pragma unroll
+        for (int i = 0; i < NN; ++i) M[i] = S[stencilIndex<N>(n, NST / 2, i)];
+#pragma unroll
+        for (int c = 0; c < N; ++c) tt[c] = b[size_t(n) * N + c] - acc[c];
+        gsNodeUpdate<N>(tt, M, dmask[n], forward != 0, u, n);
+    }
 }
 
 } // namespace vfem

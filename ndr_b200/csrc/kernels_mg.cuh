@@ -72,7 +72,7 @@ static __global__ void __launch_bounds__(kBlock) buildLevel1StencilKernel(Grid<N
     constexpr int NPE = 1 << N, KS = N * NPE, NST = ipow3(N);
     long long t = (long long)blockIdx.x * kBlock + threadIdx.x;
     if (t >= (long long)gc.nn * NST) return;
-    const int n = int(t % gc.nn), k = int(t / gc.nn);
+    const int n = int(t / NST), k = int(t % NST);
     int ci[N]; unflattenNode<N>(gc, n, ci);
     int dl[N];
     { int tt = k; for (int d = N - 1; d >= 0; --d) { dl[d] = tt % 3 - 1; tt /= 3; } }
@@ -102,7 +102,7 @@ static __global__ void __launch_bounds__(kBlock) buildLevel1StencilKernel(Grid<N
         }
     }
 #pragma unroll
-    for (int i = 0; i < N * N; ++i) S[size_t(k * N * N + i) * gc.nn + n] = blk[i];
+    for (int i = 0; i < N * N; ++i) S[stencilIndex<N>(n, k, i)] = blk[i];
 }
 
 // ---- Galerkin coarsening of a block stencil: S_c = P^T S_f P (MG.hh:659-665 assembled) ------------
@@ -111,7 +111,7 @@ static __global__ void __launch_bounds__(kBlock) galerkinStencilKernel(Grid<N> g
     constexpr int NST = ipow3(N);
     long long t = (long long)blockIdx.x * kBlock + threadIdx.x;
     if (t >= (long long)gc.nn * NST) return;
-    const int n = int(t % gc.nn), k = int(t / gc.nn);
+    const int n = int(t / NST), k = int(t % NST);
     int ci[N]; unflattenNode<N>(gc, n, ci);
     int D[N]; bool Jok = true;
     { int tt = k; for (int d = N - 1; d >= 0; --d) { D[d] = tt % 3 - 1; tt /= 3; int v = ci[d] + D[d]; Jok = Jok && v >= 0 && v < gc.n[d]; } }
@@ -139,12 +139,12 @@ static __global__ void __launch_bounds__(kBlock) galerkinStencilKernel(Grid<N> g
                 }
                 if (!okj) continue;
 #pragma unroll
-                for (int i = 0; i < N * N; ++i) blk[i] = fma(w, Sf[size_t(kj * N * N + i) * gf.nn + fn], blk[i]);
+                for (int i = 0; i < N * N; ++i) blk[i] = fma(w, Sf[stencilIndex<N>(fn, kj, i)], blk[i]);
             }
         }
     }
 #pragma unroll
-    for (int i = 0; i < N * N; ++i) Sc[size_t(k * N * N + i) * gc.nn + n] = blk[i];
+    for (int i = 0; i < N * N; ++i) Sc[stencilIndex<N>(n, k, i)] = blk[i];
 }
 
 // ---- coarsest level: dense Dirichlet-reduced matrix (TPS.hh:589-625,849: rows/cols of fixed dofs
@@ -155,7 +155,7 @@ static __global__ void __launch_bounds__(kBlock) assembleDenseKernel(Grid<N> g, 
     constexpr int NST = ipow3(N);
     long long t = (long long)blockIdx.x * kBlock + threadIdx.x;
     if (t >= (long long)g.nn * NST) return;
-    const int n = int(t % g.nn), k = int(t / g.nn);
+    const int n = int(t / NST), k = int(t % NST);
     int idx[N]; unflattenNode<N>(g, n, idx);
     int off = 0; bool ok = true;
     { int tt = k; for (int d = N - 1; d >= 0; --d) { int dl = tt % 3 - 1; tt /= 3; int v = idx[d] + dl; ok = ok && v >= 0 && v < g.n[d]; off += dl * g.ninc[d]; } }
@@ -168,7 +168,7 @@ static __global__ void __launch_bounds__(kBlock) assembleDenseKernel(Grid<N> g, 
 #pragma unroll
         for (int b = 0; b < N; ++b) {
             size_t row = size_t(n) * N + a, col = size_t(m) * N + b;
-            Real v = S[size_t(k * N * N + a * N + b) * g.nn + n];
+            Real v = S[stencilIndex<N>(n, k, a * N + b)];
             if (((mn >> a) & 1u) || ((mm >> b) & 1u)) v = (row == col) ? 1.0 : 0.0;
             A[row * nd + col] = v;
         }

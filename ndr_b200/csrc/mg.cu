@@ -2,11 +2,13 @@
 #include "mg.h"
 #include "kernels.cuh"
 #include "kernels_mg.cuh"
+#include "coarse_solve.cuh"
+#include <cublas_v2.h>
 #include <cusolverDn.h>
 
 namespace vfem {
 
-static const size_t kMaxCoarseDofs = 12288; // dense inverse: 1.2 GB at the limit
+static const size_t kMaxCoarseBytes = size_t(16) << 30; // block factors of the coarsest level
 
 #define VFEM_CUSOLVER(call)                                                                              \
     do {                                                                                                 \
@@ -71,6 +73,7 @@ template <int N>
 MG<N>::~MG() {
     if (h_scal) cudaFreeHost(h_scal);
     if (cusolverHandle) cusolverDnDestroy((cusolverDnHandle_t)cusolverHandle);
+    if (cublasHandle) cublasDestroy((cublasHandle_t)cublasHandle);
 }
 
 template <int N>
@@ -126,52 +129,69 @@ void MG<N>::updateElementStiffnessMatrices(bool force) {
         galerkinStencilKernel<N><<<unsigned((tot + kBlock - 1) / kBlock), kBlock, 0, stream>>>(lv[l - 1].g, lv[l].g, lv[l - 1].S.p, lv[l].S.p);
         VFEM_CHECK_LAUNCH(); countLaunch();
     }
-    // coarsest level: dense inverse of the Dirichlet-reduced operator
+    // coarsest level: block-tridiagonal Cholesky of the Dirichlet-reduced operator (coarse_solve.cuh)
     const Level &Lc = lv[L];
     const size_t nd = size_t(Lc.g.nn) * N;
-    if (nd > kMaxCoarseDofs)
-        throw std::runtime_error("coarsest multigrid level has " + std::to_string(nd) + " dofs; the device path solves it through a dense inverse "
-                                 "and needs <= " + std::to_string(kMaxCoarseDofs) + " (use more coarsening levels)");
-    coarseDofs = int(nd);
-    d_Ainv.alloc(nd * nd);
-    d_Ainv.zero(stream);
+    const int P = Lc.g.ninc[0] * N, planes = Lc.g.n[0];
+    const size_t PP = size_t(P) * P;
+    if (PP * size_t(3 * planes - 1) * sizeof(Real) > kMaxCoarseBytes)
+        throw std::runtime_error("coarsest multigrid level has " + std::to_string(nd) + " dofs in planes of " + std::to_string(P) +
+                                 "; its block factorisation would need " + std::to_string(PP * size_t(3 * planes - 1) * sizeof(Real) >> 20) +
+                                 " MB (use more coarsening levels)");
+    coarseDofs = int(nd); coarseP = P; coarsePlanes = planes;
+    { int rp = ((P + 31) / 32) * 32; coarseGroups = kTriThreads / (rp < kTriThreads ? rp : kTriThreads); if (coarseGroups < 1) coarseGroups = 1; }
+    d_blkD.alloc(PP * planes); d_blkW.alloc(PP * planes); d_blkLo.alloc(PP * size_t(planes > 1 ? planes - 1 : 1));
+    d_blkD.zero(stream); d_blkLo.zero(stream);
     {
         long long tot = (long long)Lc.g.nn * NST;
-        assembleDenseKernel<N><<<unsigned((tot + kBlock - 1) / kBlock), kBlock, 0, stream>>>(Lc.g, Lc.S.p, Lc.d_dmask.p, d_Ainv.p);
+        assembleBlockTriKernel<N><<<unsigned((tot + 127) / 128), 128, 0, stream>>>(Lc.g, Lc.S.p, Lc.d_dmask.p, d_blkD.p, d_blkLo.p, P);
+        VFEM_CHECK_LAUNCH(); countLaunch();
+        setIdentityBlocksKernel<<<296, 256, 0, stream>>>(d_blkW.p, P, planes);
         VFEM_CHECK_LAUNCH(); countLaunch();
     }
     if (!cusolverHandle) {
-        cusolverDnHandle_t hnd;
-        VFEM_CUSOLVER(cusolverDnCreate(&hnd));
-        cusolverHandle = hnd;
+        cusolverDnHandle_t hnd; VFEM_CUSOLVER(cusolverDnCreate(&hnd)); cusolverHandle = hnd;
+        cublasHandle_t bh; if (cublasCreate(&bh) != CUBLAS_STATUS_SUCCESS) throw std::runtime_error("cublasCreate failed"); cublasHandle = bh;
     }
     cusolverDnHandle_t hnd = (cusolverDnHandle_t)cusolverHandle;
+    cublasHandle_t bh = (cublasHandle_t)cublasHandle;
     VFEM_CUSOLVER(cusolverDnSetStream(hnd, stream));
-    int lw1 = 0, lw2 = 0;
-    VFEM_CUSOLVER(cusolverDnDpotrf_bufferSize(hnd, CUBLAS_FILL_MODE_LOWER, int(nd), d_Ainv.p, int(nd), &lw1));
-    VFEM_CUSOLVER(cusolverDnDpotri_bufferSize(hnd, CUBLAS_FILL_MODE_LOWER, int(nd), d_Ainv.p, int(nd), &lw2));
-    const int lw = lw1 > lw2 ? lw1 : lw2;
+    if (cublasSetStream(bh, stream) != CUBLAS_STATUS_SUCCESS) throw std::runtime_error("cublasSetStream failed");
+    int lw = 0;
+    VFEM_CUSOLVER(cusolverDnDpotrf_bufferSize(hnd, CUBLAS_FILL_MODE_LOWER, P, d_blkD.p, P, &lw));
     if (d_solverWork.n < size_t(lw)) d_solverWork.alloc(size_t(lw));
-    VFEM_CUSOLVER(cusolverDnDpotrf(hnd, CUBLAS_FILL_MODE_LOWER, int(nd), d_Ainv.p, int(nd), d_solverWork.p, lw, d_info.p));
-    int info = 0;
-    VFEM_CUDA(cudaMemcpyAsync(&info, d_info.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
-    VFEM_CUDA(cudaStreamSynchronize(stream));
-    if (info != 0) throw std::runtime_error("Cholesky factorization failed: coarsest-level matrix not positive definite (info " + std::to_string(info) + ")");
-    VFEM_CUSOLVER(cusolverDnDpotri(hnd, CUBLAS_FILL_MODE_LOWER, int(nd), d_Ainv.p, int(nd), d_solverWork.p, lw, d_info.p));
-    {
-        dim3 blk(32, 8), grd(unsigned((nd + 31) / 32), unsigned((nd + 7) / 8));
-        symmetrizeKernel<<<grd, blk, 0, stream>>>(d_Ainv.p, int(nd));
-        VFEM_CHECK_LAUNCH(); countLaunch();
+    if (d_info.n < size_t(planes)) d_info.alloc(size_t(planes));
+    const Real one = 1.0, mone = -1.0;
+    for (int p = 0; p < planes; ++p) {
+        Real *Dp = d_blkD.p + PP * p, *Wp = d_blkW.p + PP * p;
+        VFEM_CUSOLVER(cusolverDnDpotrf(hnd, CUBLAS_FILL_MODE_LOWER, P, Dp, P, d_solverWork.p, lw, d_info.p + p));
+        // W_p = C_p^{-1}: solve C_p X = I
+        if (cublasDtrsm(bh, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, P, P, &one, Dp, P, Wp, P) != CUBLAS_STATUS_SUCCESS)
+            throw std::runtime_error("cublasDtrsm failed");
+        if (p + 1 < planes) {
+            Real *Lp = d_blkLo.p + PP * p, *Dn = d_blkD.p + PP * (p + 1);
+            // L_p = A_{p+1,p} C_p^{-T};  D_{p+1} -= L_p L_p^T
+            if (cublasDtrsm(bh, CUBLAS_SIDE_RIGHT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_T, CUBLAS_DIAG_NON_UNIT, P, P, &one, Dp, P, Lp, P) != CUBLAS_STATUS_SUCCESS)
+                throw std::runtime_error("cublasDtrsm failed");
+            if (cublasDsyrk(bh, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, P, P, &mone, Lp, P, &one, Dn, P) != CUBLAS_STATUS_SUCCESS)
+                throw std::runtime_error("cublasDsyrk failed");
+        }
+        countLaunch(3);
     }
+    std::vector<int> info(planes, 0);
+    VFEM_CUDA(cudaMemcpyAsync(info.data(), d_info.p, sizeof(int) * planes, cudaMemcpyDeviceToHost, stream));
+    VFEM_CUDA(cudaStreamSynchronize(stream));
+    for (int p = 0; p < planes; ++p)
+        if (info[p] != 0) throw std::runtime_error("Cholesky factorization failed: coarsest-level matrix not positive definite (plane " + std::to_string(p) + ", info " + std::to_string(info[p]) + ")");
     builtVersion = sim->densityVersion;
 }
 
 template <int N>
 void MG<N>::coarseSolve(const Real *b, Real *x) {
     const Level &Lc = lv.back();
-    const int nd = coarseDofs;
-    const int threads = 128, rowsPerBlock = threads / 32;
-    denseSolveKernel<N><<<(nd + rowsPerBlock - 1) / rowsPerBlock, threads, 0, stream>>>(d_Ainv.p, b, Lc.d_dmask.p, x, nd);
+    const size_t smem = size_t(3 + coarseGroups) * coarseP * sizeof(Real);
+    if (smem > 48 * 1024) VFEM_CUDA(cudaFuncSetAttribute(blockTriSolveKernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    blockTriSolveKernel<N><<<1, kTriThreads, smem, stream>>>(coarseP, coarsePlanes, d_blkW.p, d_blkLo.p, b, Lc.d_dmask.p, x, coarseGroups);
     VFEM_CHECK_LAUNCH(); countLaunch();
 }
 
@@ -187,7 +207,8 @@ void MG<N>::applyMode(size_t l, const Real *u, const Real *b, Real *out) {
     const Level &L = lv.at(l);
     const unsigned blocks = unsigned((L.g.nn + kBlock - 1) / kBlock);
     if (l == 0) { sim->template applyFine<MODE>(u, b, maskOf(*this, 0), out); return; }
-    applyStencilKernel<N, MODE><<<blocks, kBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), out);
+    (void)blocks;
+    applyStencilWarpKernel<N, MODE><<<unsigned((size_t(L.g.nn) * 32 + kWarpBlock - 1) / kWarpBlock), kWarpBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), out);
     VFEM_CHECK_LAUNCH(); countLaunch();
 }
 
@@ -204,7 +225,7 @@ void MG<N>::smoothColoured(size_t l, Real *u, const Real *b, bool forward) {
         const int cnt = colourCount<N>(L.g, colour);
         const unsigned blocks = unsigned((cnt + kBlock - 1) / kBlock);
         if (l == 0) gsFineKernel<N><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
-        else gsStencilKernel<N><<<blocks, kBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), colour, forward ? 1 : 0);
+        else gsStencilWarpKernel<N><<<unsigned((size_t(cnt) * 32 + kWarpBlock - 1) / kWarpBlock), kWarpBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), colour, forward ? 1 : 0);
         VFEM_CHECK_LAUNCH(); countLaunch();
     }
 }

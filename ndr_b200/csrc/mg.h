@@ -5,8 +5,9 @@
 // Galerkin operator P^T K P as an assembled 3^N-point block stencil in SoA layout.  The reference
 // keeps a dense 24x24 Ke per coarse element (4.6 KB each) AND a block-CSC matrix per level; the
 // assembled stencil is the same linear operator, so smoothing/apply/restriction results agree to
-// roundoff.  The coarsest level is solved exactly through a dense inverse (cuSOLVER potrf/potri,
-// refreshed once per density update) applied as one GEMV, where the reference calls CHOLMOD.
+// roundoff.  The coarsest level is solved exactly through a block-tridiagonal Cholesky factorisation over
+// its node planes (cuSOLVER potrf + cuBLAS trsm/syrk per plane, refreshed once per density update) whose
+// solves are one kernel launch each (coarse_solve.cuh), where the reference calls CHOLMOD.
 #pragma once
 #include "sim.h"
 #include "kernels_vec.cuh"
@@ -33,8 +34,11 @@ struct MG : MGBase {
     std::shared_ptr<Sim<N>> sim;
     std::vector<Level> lv;
     DevBuf<Real> d_C;               // 2^N coarsened reference stiffness matrices (MG.hh:644-648)
-    DevBuf<Real> d_Ainv;            // dense inverse of the coarsest Dirichlet-reduced operator
+    // coarsest level: block-tridiagonal Cholesky over the node planes of axis 0 (coarse_solve.cuh)
+    DevBuf<Real> d_blkD, d_blkW, d_blkLo; // C_p (potrf of the diagonal blocks), W_p = C_p^{-1}, L_p
+    int coarseP = 0, coarsePlanes = 0, coarseGroups = 1;
     int coarseDofs = 0;
+    void *cublasHandle = nullptr;
     unsigned long long builtVersion = 0;
     bool symmetricGS = true;                       // MG.hh:758
     bool buildBlockStiffnessMatrices = true;       // MG.hh:746 (kept for API parity; no effect on results)
