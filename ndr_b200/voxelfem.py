@@ -108,7 +108,7 @@ class TensorProductSimulator:
         self._elems = [int(e) for e in el]
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:  # `lib` is None during interpreter shutdown
             lib().vfem_tps_destroy(self._h)
             self._h = None
 

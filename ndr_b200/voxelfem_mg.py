@@ -41,7 +41,7 @@ class MultigridSolver:
         self._flags = [True, False]
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:
             lib().vfem_mg_destroy(self._h)
             self._h = None
 
@@ -187,7 +187,7 @@ class MultigridComplianceObjective:
         check(lib().vfem_obj_create(mg_solver._h, C.byref(self._h)))
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:
             lib().vfem_obj_destroy(self._h)
             object.__setattr__(self, "_h", None)
 

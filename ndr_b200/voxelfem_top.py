@@ -108,7 +108,7 @@ class TopologyOptimizationProblem:
             f._owner = (self, i)
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:
             lib().vfem_top_destroy(self._h)
             self._h = None
 
