@@ -88,6 +88,10 @@ int vfem_mg_restrict(vfem_mg_t h, size_t l_fine, const double *v_fine, double *o
 int vfem_mg_interpolate(vfem_mg_t h, size_t l_fine, const double *x_coarse, double *x_fine, int accumulate, int memspace); /* MG.hh:115-141 */
 int vfem_mg_level_stencil(vfem_mg_t h, size_t l, double *out);                      /* debug: assembled operator of level l >= 1, (3^N, N, N, nn) */
 int vfem_mg_debug_get(vfem_mg_t h, size_t l, double *x, double *b);                 /* debug_get_x / debug_get_b */
+/* profiling hook (no reference counterpart): average device time of one operator of level l over `reps` back-to-back calls.
+ * op: 0 one forward GS sweep, 1 residual, 2 restriction l->l+1, 3 prolongation l+1->l, 4 coarsest solve, 5 operator refresh,
+ * 6 one FMG preconditioner pass (2 sweeps), 7 masked K u */
+int vfem_mg_time_op(vfem_mg_t h, int op, size_t l, int reps, double *ms_per_call);
 typedef void (*vfem_solve_cb)(void *ctx, size_t it, const double *x_host);
 int vfem_mg_solve(vfem_mg_t h, const double *u, const double *f, size_t num_steps, size_t num_smoothing_steps, int stiffness_updated,
                   int zero_dirichlet, vfem_solve_cb cb, void *cb_ctx, int full_multigrid, double *out, int memspace); /* solve (MG.hh:446-472) */

@@ -57,6 +57,35 @@ int vfem_mg_level_stencil(vfem_mg_t h, size_t l, double *out) {
 int vfem_mg_debug_get(vfem_mg_t h, size_t l, double *x, double *b) {
     API_TRY WITH_MG(h, if (x) mg.lv.at(l).x.download(x, mg.stream); if (b) mg.lv.at(l).b.download(b, mg.stream);); API_CATCH }
 
+int vfem_mg_time_op(vfem_mg_t h, int op, size_t l, int reps, double *ms_per_call) {
+    API_TRY WITH_MG(h,
+        mg.syncMasks(); mg.updateElementStiffnessMatrices(false);
+        auto &L = mg.lv.at(l);
+        auto run = [&]() {
+            switch (op) {
+            case 0: mg.smoothColoured(l, L.x.p, L.b.p, true); break;
+            case 1: mg.computeResidual(l, L.x.p, L.b.p, L.r.p); break;
+            case 2: mg.restriction(l, L.r.p, mg.lv.at(l + 1).b.p); break;
+            case 3: mg.interpolate(l, mg.lv.at(l + 1).x.p, L.x.p, true); break;
+            case 4: mg.coarseSolve(mg.lv.back().b.p, mg.lv.back().x.p); break;
+            case 5: mg.updateElementStiffnessMatrices(true); break;
+            case 6: mg.precondition(mg.p_r.p, 1, 2, true); break;
+            case 7: mg.applyKMasked(l, L.x.p, L.r.p); break;
+            default: throw std::runtime_error("vfem_mg_time_op: unknown op");
+            }
+        };
+        run();
+        cudaEvent_t e0; cudaEvent_t e1; VFEM_CUDA(cudaEventCreate(&e0)); VFEM_CUDA(cudaEventCreate(&e1));
+        VFEM_CUDA(cudaStreamSynchronize(mg.stream));
+        VFEM_CUDA(cudaEventRecord(e0, mg.stream));
+        for (int r = 0; r < reps; ++r) run();
+        VFEM_CUDA(cudaEventRecord(e1, mg.stream));
+        VFEM_CUDA(cudaEventSynchronize(e1));
+        float ms = 0.f; VFEM_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+        *ms_per_call = double(ms) / reps;);
+    API_CATCH }
+
 int vfem_mg_solve(vfem_mg_t h, const double *u, const double *f, size_t num_steps, size_t nu, int stiffness_updated, int zero_dirichlet,
                   vfem_solve_cb cb, void *cb_ctx, int fmg, double *out, int ms) {
     API_TRY WITH_MG(h,

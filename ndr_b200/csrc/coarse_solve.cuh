@@ -3,14 +3,20 @@
 //
 // With nodes numbered axis-0-slowest the coarsest operator is block tridiagonal over the node planes of axis 0
 // (a node only couples to the planes x-1, x, x+1): P = N * nodesPerPlane dofs per block.  Once per density update the
-// host runs a block Cholesky  A = L L^T,  L block lower bidiagonal with diagonal blocks C_p and sub-diagonal blocks
-// L_p = A_{p+1,p} C_p^{-T}  (cuSOLVER potrf + cuBLAS trsm/syrk on P x P blocks) and forms W_p = C_p^{-1} explicitly, so that
-// every solve is a chain of dense matrix-vector products done by ONE kernel launch (blockTriSolveKernel):
-//     forward   y_p = W_p (b_p - L_{p-1} y_{p-1}),      backward   x_p = W_p^T (y_p - L_p^T x_{p+1}).
-// Constrained dofs keep an identity row/column and a zero right-hand side, which gives the reduced system's solution
-// on the free dofs and 0 on the fixed ones.  All blocks are column-major (cuBLAS convention), leading dimension P.
+// host runs the block LDL^T recurrence  S_0 = A_00,  T_p = A_{p,p-1} S_{p-1}^{-1},  S_p = A_pp - T_p A_{p,p-1}^T
+// (cuSOLVER potrf + cuBLAS trsm/gemm on P x P blocks) and stores S_p^{-1}, T_p explicitly, so that a solve is
+//     forward    z_p = b_p - T_p z_{p-1}            (a chain of planes-1 dependent matrix-vector products)
+//     diagonal   v_p = S_p^{-1} z_p                 (independent over the planes)
+//     backward   x_p = v_p - T_{p+1}^T x_{p+1}      (a chain again)
+// done by ONE launch of ONE thread-block cluster (blockTriChainKernel): the rows of each product are spread over the
+// warps of the cluster, every CTA keeps the current plane vector in its shared memory, and a finished entry is written
+// into all CTAs' copies through distributed shared memory, so a chain step costs one cluster barrier instead of a
+// kernel launch or a grid-wide barrier.  Constrained dofs keep an identity row/column and a zero right-hand side,
+// which gives the reduced system's solution on the free dofs and 0 on the fixed ones.
+// Blocks handed to cuBLAS are column-major with leading dimension P; Trm/Sinv are read row-wise, Tcm column-wise.
 #pragma once
 #include "common.h"
+#include <cooperative_groups.h>
 
 namespace vfem {
 
@@ -50,80 +56,119 @@ static __global__ void setIdentityBlocksKernel(Real *__restrict__ W, int P, int 
     }
 }
 
-constexpr int kTriThreads = 1024;
+constexpr int kChainThreads = 512; // per CTA
+constexpr int kChainCluster = 8;   // portable cluster size
 
-// One CTA walks the planes; see the header comment.  W: C_p^{-1} (lower triangular, col-major), Lo: L_p.
-// dynamic shared memory: (3 + groups) * P doubles.
-template <int N>
-static __global__ void __launch_bounds__(kTriThreads) blockTriSolveKernel(int P, int planes, const Real *__restrict__ W, const Real *__restrict__ Lo,
-                                                                          const Real *__restrict__ b, const uint8_t *__restrict__ dmask,
-                                                                          Real *__restrict__ x, int groups) {
+// dot products of up to two matrix rows with the shared vector (lane-strided, fixed order) + shuffle tree
+__device__ __forceinline__ void chainRows2(const Real *__restrict__ r0, const Real *__restrict__ r1, bool two, const Real *v, int P, int lane,
+                                           Real &s0, Real &s1) {
+    Real a0 = 0.0, a1 = 0.0;
+    for (int j = lane; j < P; j += 32) {
+        const Real vj = v[j];
+        a0 = fma(r0[j], vj, a0);
+        if (two) a1 = fma(r1[j], vj, a1);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { a0 += __shfl_xor_sync(0xffffffffu, a0, o); a1 += __shfl_xor_sync(0xffffffffu, a1, o); }
+    s0 = a0; s1 = a1;
+}
+
+// One cluster walks the planes; see the header comment.  Trm[p-1]: T_p row-major, Tcm[p-1]: T_p column-major (p = 1..planes-1),
+// Sinv[p]: S_p^{-1}.  x doubles as the scratch for v; z: planes*P scratch.  Dynamic shared memory: 2*P doubles.
+// PF (P <= 2 rows per warp, <= 256 columns): the matrix rows of the NEXT chain step are fetched into registers before
+// the cluster barrier of the current one, so the L2/HBM latency of the (vector-independent) matrix overlaps the barrier.
+template <int N, bool PF>
+static __global__ void __launch_bounds__(kChainThreads) blockTriChainKernel(int P, int planes, const Real *__restrict__ Trm, const Real *__restrict__ Tcm,
+                                                                            const Real *__restrict__ Sinv, const Real *__restrict__ b,
+                                                                            const uint8_t *__restrict__ dmask, Real *x, Real *z) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cl = cg::this_cluster();
     extern __shared__ Real sm[];
-    Real *cur = sm, *prev = sm + P, *tmp = sm + 2 * P, *part = sm + 3 * P; // part[groups][P]
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = kTriThreads / 32;
-    const int rowsPerPass = kTriThreads / groups; // threads per column group
-    const int gq = tid / rowsPerPass, r0 = tid - gq * rowsPerPass;
+    Real *cur = sm, *nxt = sm + P;
+    const int tid = threadIdx.x, lane = tid & 31, nw = kChainThreads / 32;
+    const int ncta = int(cl.num_blocks()), rank = int(cl.block_rank());
+    const int gw = rank * nw + (tid >> 5), tw = ncta * nw;
     const size_t PP = size_t(P) * P;
-    // ---- forward: y_p = W_p (b_p - L_{p-1} y_{p-1}) ----
-    for (int p = 0; p < planes; ++p) {
-        const Real *Lp = (p > 0) ? Lo + size_t(p - 1) * PP : Lo, *Wp = W + size_t(p) * PP;
-        // tmp = b_p (masked) - L_{p-1} prev : column groups -> partial sums, fixed-order reduction
-        if (p > 0 && gq < groups) {
-            for (int i = r0; i < P; i += rowsPerPass) {
-                Real s = 0.0;
-                for (int j = gq; j < P; j += groups) s = fma(Lp[size_t(i) + size_t(j) * P], prev[j], s);
-                part[gq * P + i] = s;
-            }
-        }
-        __syncthreads();
-        for (int i = tid; i < P; i += kTriThreads) {
-            const int dof = p * P + i;
-            Real v = ((dmask[dof / N] >> (dof % N)) & 1u) ? 0.0 : b[dof];
-            if (p > 0) for (int q = 0; q < groups; ++q) v -= part[q * P + i];
-            tmp[i] = v;
-        }
-        __syncthreads();
-        if (gq < groups) {
-            for (int i = r0; i < P; i += rowsPerPass) {
-                Real s = 0.0;
-                for (int j = gq; j <= i; j += groups) s = fma(Wp[size_t(i) + size_t(j) * P], tmp[j], s);
-                part[gq * P + i] = s;
-            }
-        }
-        __syncthreads();
-        for (int i = tid; i < P; i += kTriThreads) {
-            Real v = 0.0;
-            for (int q = 0; q < groups; ++q) v += part[q * P + i];
-            cur[i] = v; x[p * P + i] = v; // y_p parked in x
-        }
-        __syncthreads();
-        Real *sw = cur; cur = prev; prev = sw; // prev = y_p
-    }
-    // ---- backward: x_p = W_p^T (y_p - L_p^T x_{p+1});  prev holds x_{p+1} ----
-    for (int p = planes - 1; p >= 0; --p) {
-        const Real *Lp = Lo + size_t(p) * PP, *Wp = W + size_t(p) * PP;
-        for (int j = warp; j < P; j += nwarps) { // tmp_j = y_j - column_j(L_p) . x_{p+1}
-            Real s = 0.0;
-            if (p < planes - 1) for (int i = lane; i < P; i += 32) s = fma(Lp[size_t(i) + size_t(j) * P], prev[i], s);
+    auto masked = [&](int dof, Real v) { return ((dmask[dof / N] >> (dof % N)) & 1u) ? 0.0 : v; };
+    // every entry is published to all CTAs' copies of the next plane vector (lanes 0..ncta-1 each serve one CTA)
+    auto publish = [&](int i, Real v) {
+        if (lane < ncta) cl.map_shared_rank(nxt, lane)[i] = v;
+    };
+    constexpr int JP = 8;
+    Real t0[JP], t1[JP];
+    const bool has0 = gw < P, has1 = gw + tw < P;
+    auto fetch = [&](const Real *T) { // rows gw and gw + tw of T
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            if (lane == 0) tmp[j] = x[p * P + j] - s;
+        for (int j = 0; j < JP; ++j) {
+            const int c = lane + 32 * j;
+            t0[j] = (has0 && c < P) ? T[size_t(gw) * P + c] : 0.0;
+            t1[j] = (has1 && c < P) ? T[size_t(gw + tw) * P + c] : 0.0;
         }
-        __syncthreads();
-        for (int j = warp; j < P; j += nwarps) { // x_j = column_j(W_p)[j:] . tmp[j:]
-            Real s = 0.0;
-            for (int i = j + lane; i < P; i += 32) s = fma(Wp[size_t(i) + size_t(j) * P], tmp[i], s);
+    };
+    auto dots = [&](Real &s0, Real &s1) {
+        Real a0 = 0.0, a1 = 0.0;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            if (lane == 0) {
-                const int dof = p * P + j;
-                const Real v = ((dmask[dof / N] >> (dof % N)) & 1u) ? 0.0 : s;
-                cur[j] = v; x[dof] = v;
+        for (int j = 0; j < JP; ++j) {
+            const int c = lane + 32 * j;
+            const Real vj = c < P ? cur[c] : 0.0;
+            a0 = fma(t0[j], vj, a0); a1 = fma(t1[j], vj, a1);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { a0 += __shfl_xor_sync(0xffffffffu, a0, o); a1 += __shfl_xor_sync(0xffffffffu, a1, o); }
+        s0 = a0; s1 = a1;
+    };
+    // one chain step: out_p[i] = masked(rhs[p*P+i] - row_i(T) . cur), published to every CTA and stored to `store`
+    auto chainStep = [&](const Real *T, const Real *rhs, Real *store, int p, const Real *Tnext) {
+        if (PF) {
+            Real s0, s1;
+            dots(s0, s1);
+            if (has0) { const Real v = masked(p * P + gw, rhs[p * P + gw] - s0); publish(gw, v); if (lane == 0) store[p * P + gw] = v; }
+            if (has1) { const Real v = masked(p * P + gw + tw, rhs[p * P + gw + tw] - s1); publish(gw + tw, v); if (lane == 0) store[p * P + gw + tw] = v; }
+            if (Tnext) fetch(Tnext);
+        } else {
+            for (int i = gw; i < P; i += 2 * tw) {
+                const bool two = i + tw < P;
+                Real s0, s1;
+                chainRows2(T + size_t(i) * P, T + size_t(two ? i + tw : i) * P, two, cur, P, lane, s0, s1);
+                const Real v0 = masked(p * P + i, rhs[p * P + i] - s0);
+                publish(i, v0);
+                if (lane == 0) store[p * P + i] = v0;
+                if (two) {
+                    const Real v1 = masked(p * P + i + tw, rhs[p * P + i + tw] - s1);
+                    publish(i + tw, v1);
+                    if (lane == 0) store[p * P + i + tw] = v1;
+                }
             }
         }
-        __syncthreads();
-        Real *sw = cur; cur = prev; prev = sw; // prev = x_p
+        cl.sync();
+        Real *sw = cur; cur = nxt; nxt = sw;
+    };
+    // ---- forward: z_0 = b_0,  z_p = b_p - T_p z_{p-1} ----
+    if (PF && planes > 1) fetch(Trm);
+    for (int i = tid; i < P; i += kChainThreads) { const Real v = masked(i, b[i]); cur[i] = v; if (rank == 0) z[i] = v; }
+    cl.sync();
+    for (int p = 1; p < planes; ++p)
+        chainStep(Trm + size_t(p - 1) * PP, b, z, p, p + 1 < planes ? Trm + size_t(p) * PP : nullptr);
+    __threadfence();
+    cl.sync();
+    // ---- diagonal: v_p = S_p^{-1} z_p, all planes at once (v parked in x) ----
+    if (PF && planes > 1) fetch(Tcm + size_t(planes - 2) * PP);
+    for (int row = gw; row < planes * P; row += tw) {
+        const int p = row / P, i = row - p * P;
+        const Real *Sr = Sinv + size_t(p) * PP + size_t(i) * P, *zp = z + size_t(p) * P;
+        Real a = 0.0;
+        for (int j = lane; j < P; j += 32) a = fma(Sr[j], zp[j], a);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+        if (lane == 0) x[row] = masked(row, a);
     }
+    __threadfence();
+    cl.sync();
+    // ---- backward: x_last = v_last,  x_p = v_p - T_{p+1}^T x_{p+1}  (column i of T_{p+1} is contiguous in Tcm) ----
+    for (int i = tid; i < P; i += kChainThreads) cur[i] = x[size_t(planes - 1) * P + i];
+    __syncthreads();
+    for (int p = planes - 2; p >= 0; --p)
+        chainStep(Tcm + size_t(p) * PP, x, x, p, p > 0 ? Tcm + size_t(p - 1) * PP : nullptr);
 }
 
 } // namespace vfem

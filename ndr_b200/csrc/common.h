@@ -96,9 +96,11 @@ struct K0Param {
 
 constexpr int ipow3(int n) { return n == 0 ? 1 : 3 * ipow3(n - 1); }
 
-// assembled coarse-level operator, node-major: entry (a,b) (i = a*N+b) of the block coupling node n to neighbour slot k
+// assembled coarse-level operator, node-major, one matrix row after the other: entry (a,b) (i = a*N+b) of the block
+// coupling node n to neighbour slot k sits at ((n*N + a)*3^N + k)*N + b, so row a of node n is 3^N*N contiguous doubles
+// that line up with the neighbour values u[n+delta(k)][b]
 template <int N>
-__host__ __device__ __forceinline__ size_t stencilIndex(int n, int k, int i) { return (size_t(n) * ipow3(N) + k) * (N * N) + i; }
+__host__ __device__ __forceinline__ size_t stencilIndex(int n, int k, int i) { return ((size_t(n) * N + i / N) * ipow3(N) + k) * N + (i % N); }
 
 enum MemSpace { MS_HOST = 0, MS_DEVICE = 1 };
 

@@ -106,64 +106,54 @@ __device__ __forceinline__ void fineNodeRow(const Grid<N> &g, const K0Param<N> &
 }
 
 // ---- coarse levels: assembled 3^N-point block stencil ---------------------------------------------
-// Node-major: S[(n*3^N + k)*N*N + a*N + b] = K_l[(n,a), (n + delta(k), b)] (zero for out-of-grid neighbours),
-// so the 3^N * N * N coefficients of one node are contiguous and a warp reads them fully coalesced.
+// Node-major, row after row: S[((n*N + a)*3^N + k)*N + b] = K_l[(n,a), (n + delta(k), b)] (zero for out-of-grid
+// neighbours), so the 3^N * N * N coefficients of one node are contiguous and a warp reads them fully coalesced.
 
 // The reference stores the same operator as a block-CSC matrix (TPS.hh:649-720) and applies it
 // with applyTransposeParallel (SparseMatrices.hh:1519-1568).
-template <int N, bool WITH_M>
-__device__ __forceinline__ void stencilNodeRow(const Grid<N> &g, const Real *__restrict__ S, const Real *__restrict__ u,
-                                               const int *idx, int n, Real *acc, Real *M) {
-    constexpr int NST = ipow3(N);
-#pragma unroll
-    for (int k = 0; k < NST; ++k) {
-        int t = k, off = 0; bool ok = true;
-#pragma unroll
-        for (int d = N - 1; d >= 0; --d) {
-            int dl = t % 3 - 1; t /= 3;
-            int v = idx[d] + dl; ok = ok && (v >= 0) && (v < g.n[d]);
-            off += dl * g.ninc[d];
-        }
-        Real um[N];
-#pragma unroll
-        for (int b = 0; b < N; ++b) um[b] = ok ? u[size_t(n + off) * N + b] : 0.0;
-#pragma unroll
-        for (int a = 0; a < N; ++a)
-#pragma unroll
-            for (int b = 0; b < N; ++b) {
-                Real s = S[stencilIndex<N>(n, k, a * N + b)];
-                acc[a] = fma(s, um[b], acc[a]);
-                if (WITH_M && k == NST / 2) M[a * N + b] = s;
-            }
-    }
-}
 
-// Warp-per-node row of the assembled operator: the node's 3^N*N*N coefficients are read coalesced (lane l takes
-// entries l, l+32, ...), each multiplied with the neighbour value it belongs to, and the N partial row sums are
-// combined with a fixed shuffle tree (deterministic).  All lanes return the full row sums.
+// Warp-per-node rows of the assembled operator.  Lane l owns the row entries e = l, l+32, ... (< 3^N*N) of every
+// matrix row; entry e multiplies u[n + delta(e / N)][e % N], an address offset that depends on the lane only, so it is
+// computed once per warp (StencilLane) and reused for all nodes and all N rows.  Out-of-grid neighbours have zero
+// coefficients (buildLevel1StencilKernel / galerkinStencilKernel), so their addresses are clamped instead of tested.
+// The N partial row sums are combined with a fixed shuffle tree (deterministic); all lanes return the full sums.
 template <int N>
-__device__ __forceinline__ void stencilWarpRow(const Grid<N> &g, const Real *__restrict__ S, const Real *__restrict__ u, const int *idx,
-                                               int n, int lane, Real *acc) {
-    constexpr int NST = ipow3(N), NN = N * N, TOT = NST * NN;
-    const Real *Sn = S + size_t(n) * TOT;
+struct StencilLane {
+    static constexpr int ROW = ipow3(N) * N, J = (ROW + 31) / 32;
+    int uoff[J];   // dof offset of the neighbour value relative to n*N
+    bool valid[J];
+    __device__ __forceinline__ void init(const Grid<N> &g, int lane) {
 #pragma unroll
-    for (int a = 0; a < N; ++a) acc[a] = 0.0;
+        for (int j = 0; j < J; ++j) {
+            const int e = lane + 32 * j;
+            valid[j] = e < ROW;
+            const int k = valid[j] ? e / N : 0, b = valid[j] ? e % N : 0;
+            int t = k, off = 0;
 #pragma unroll
-    for (int j = 0; j < (TOT + 31) / 32; ++j) {
-        const int e = lane + 32 * j;
-        if (e < TOT) {
-            const int k = e / NN, ab = e - k * NN, a = ab / N, b = ab - a * N;
-            int t = k, off = 0; bool ok = true;
-#pragma unroll
-            for (int d = N - 1; d >= 0; --d) {
-                int dl = t % 3 - 1; t /= 3;
-                int v = idx[d] + dl; ok = ok && (v >= 0) && (v < g.n[d]);
-                off += dl * g.ninc[d];
-            }
-            const Real p = ok ? Sn[e] * u[size_t(n + off) * N + b] : 0.0;
-#pragma unroll
-            for (int a2 = 0; a2 < N; ++a2) acc[a2] += (a2 == a) ? p : 0.0;
+            for (int d = N - 1; d >= 0; --d) { off += (t % 3 - 1) * g.ninc[d]; t /= 3; }
+            uoff[j] = off * N + b;
         }
+    }
+};
+
+template <int N>
+__device__ __forceinline__ void stencilWarpRow(const StencilLane<N> &sl, int ndof, const Real *__restrict__ S, const Real *__restrict__ u, int n,
+                                               int lane, Real *acc) {
+    constexpr int ROW = StencilLane<N>::ROW, J = StencilLane<N>::J;
+    const Real *Sn = S + size_t(n) * N * ROW + lane;
+    Real uv[J];
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+        const int a = min(max(n * N + sl.uoff[j], 0), ndof - 1);
+        uv[j] = sl.valid[j] ? u[a] : 0.0;
+    }
+#pragma unroll
+    for (int a = 0; a < N; ++a) {
+        Real s = 0.0;
+#pragma unroll
+        for (int j = 0; j < J; ++j)
+            if (sl.valid[j]) s = fma(Sn[a * ROW + 32 * j], uv[j], s);
+        acc[a] = s;
     }
 #pragma unroll
     for (int a = 0; a < N; ++a)
@@ -173,20 +163,26 @@ __device__ __forceinline__ void stencilWarpRow(const Grid<N> &g, const Real *__r
 
 // Gauss-Seidel update of one node (MG.hh:248-264): t = b_n - (K u)_n, then one component-wise
 // forward/backward substitution through the diagonal block M; constrained components get 0.
-template <int N>
-__device__ __forceinline__ void gsNodeUpdate(const Real *t, const Real *M, unsigned mask, bool forward, Real *__restrict__ u, int n) {
-    Real du[N];
+template <int N, bool FWD>
+__device__ __forceinline__ void gsNodeSubst(const Real *t, const Real *M, unsigned mask, Real *du) {
 #pragma unroll
     for (int c = 0; c < N; ++c) du[c] = 0.0;
 #pragma unroll
     for (int ii = 0; ii < N; ++ii) {
-        const int i = forward ? ii : (N - 1 - ii);
+        constexpr int dummy = 0; (void)dummy;
+        const int i = FWD ? ii : (N - 1 - ii);
         Real s = 0.0;
 #pragma unroll
         for (int j = 0; j < N; ++j) s = fma(M[i * N + j], du[j], s);
         const Real inv = ((mask >> i) & 1u) ? 0.0 : 1.0 / M[i * N + i];
         du[i] = (t[i] - s) * inv;
     }
+}
+template <int N>
+__device__ __forceinline__ void gsNodeUpdate(const Real *t, const Real *M, unsigned mask, bool forward, Real *__restrict__ u, int n) {
+    Real du[N];
+    if (forward) gsNodeSubst<N, true>(t, M, mask, du);
+    else gsNodeSubst<N, false>(t, M, mask, du);
 #pragma unroll
     for (int c = 0; c < N; ++c) u[size_t(n) * N + c] += du[c];
 }
@@ -215,29 +211,9 @@ __global__ void __launch_bounds__(kBlock) applyFineKernel(Grid<N> g, K0Param<N> 
     }
 }
 
-template <int N, int MODE>
-__global__ void __launch_bounds__(kBlock) applyStencilKernel(Grid<N> g, const Real *__restrict__ S, const Real *__restrict__ u,
-                                                              const Real *__restrict__ b, const uint8_t *__restrict__ dmask,
-                                                              Real *__restrict__ out) {
-    int n = blockIdx.x * kBlock + threadIdx.x;
-    if (n >= g.nn) return;
-    int idx[N]; unflattenNode<N>(g, n, idx);
-    Real acc[N];
-#pragma unroll
-    for (int c = 0; c < N; ++c) acc[c] = 0.0;
-    stencilNodeRow<N, false>(g, S, u, idx, n, acc, nullptr);
-    unsigned m = (MODE != 0) ? dmask[n] : 0u;
-#pragma unroll
-    for (int c = 0; c < N; ++c) {
-        Real v = (MODE == 1) ? b[size_t(n) * N + c] - acc[c] : acc[c];
-        if ((m >> c) & 1u) v = 0.0;
-        out[size_t(n) * N + c] = v;
-    }
-}
-
 // ---- multicoloured Gauss-Seidel: one colour phase (MG.hh:284-340) --------------------------------
-template <int N>
-__global__ void __launch_bounds__(kBlock) gsFineKernel(Grid<N> g, K0Param<N> K, const Real *__restrict__ Ey, Real *__restrict__ u,
+template <int N, int MINB>
+__global__ void __launch_bounds__(kBlock, MINB) gsFineKernel(Grid<N> g, K0Param<N> K, const Real *__restrict__ Ey, Real *__restrict__ u,
                                                         const Real *__restrict__ b, const uint8_t *__restrict__ dmask, int colour,
                                                         int forward) {
     int t = blockIdx.x * kBlock + threadIdx.x;
@@ -256,66 +232,63 @@ __global__ void __launch_bounds__(kBlock) gsFineKernel(Grid<N> g, K0Param<N> K, 
     gsNodeUpdate<N>(tt, M, dmask[n], forward != 0, u, n);
 }
 
-template <int N>
-__global__ void __launch_bounds__(kBlock) gsStencilKernel(Grid<N> g, const Real *__restrict__ S, Real *__restrict__ u,
-                                                           const Real *__restrict__ b, const uint8_t *__restrict__ dmask, int colour,
-                                                           int forward) {
-    int t = blockIdx.x * kBlock + threadIdx.x;
-    int idx[N];
-    if (!colourNode<N>(g, t, colour, idx)) return;
-    int n = flattenNode<N>(g, idx);
-    Real acc[N], M[N * N];
-#pragma unroll
-    for (int c = 0; c < N; ++c) acc[c] = 0.0;
-    stencilNodeRow<N, true>(g, S, u, idx, n, acc, M);
-    Real tt[N];
-#pragma unroll
-    for (int c = 0; c < N; ++c) tt[c] = b[size_t(n) * N + c] - acc[c];
-    gsNodeUpdate<N>(tt, M, dmask[n], forward != 0, u, n);
+
+// ---- warp-per-node kernels for the assembled levels: persistent warps striding over the nodes ----
+constexpr int kWarpBlock = 256; // 8 warps per block
+inline unsigned warpGridBlocks(long long nodes) {
+    const long long need = (nodes * 32 + kWarpBlock - 1) / kWarpBlock, cap = 148 * 8;
+    return unsigned(need < cap ? (need > 0 ? need : 1) : cap);
 }
-
-
-// ---- warp-per-node variants for the assembled levels (small grids: latency- and launch-bound with one thread/node)
-constexpr int kWarpBlock = 256; // 8 nodes per block
 
 template <int N, int MODE>
 __global__ void __launch_bounds__(kWarpBlock) applyStencilWarpKernel(Grid<N> g, const Real *__restrict__ S, const Real *__restrict__ u,
                                                                       const Real *__restrict__ b, const uint8_t *__restrict__ dmask,
                                                                       Real *__restrict__ out) {
-    const int n = (blockIdx.x * kWarpBlock + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (n >= g.nn) return;
-    int idx[N]; unflattenNode<N>(g, n, idx);
-    Real acc[N];
-    stencilWarpRow<N>(g, S, u, idx, n, lane, acc);
-    if (lane < N) {
-        const unsigned m = (MODE != 0) ? dmask[n] : 0u;
-        Real v = acc[0];
+    const int lane = threadIdx.x & 31, nwarps = (gridDim.x * kWarpBlock) >> 5;
+    StencilLane<N> sl; sl.init(g, lane);
+    for (int n = (blockIdx.x * kWarpBlock + threadIdx.x) >> 5; n < g.nn; n += nwarps) {
+        Real acc[N];
+        stencilWarpRow<N>(sl, g.nn * N, S, u, n, lane, acc);
+        if (lane < N) {
+            const unsigned m = (MODE != 0) ? dmask[n] : 0u;
+            Real v = acc[0];
 #pragma unroll
-        for (int c = 1; c < N; ++c) if (lane == c) v = acc[c];
-        if (MODE == 1) v = b[size_t(n) * N + lane] - v;
-        if ((m >> lane) & 1u) v = 0.0;
-        out[size_t(n) * N + lane] = v;
+            for (int c = 1; c < N; ++c) if (lane == c) v = acc[c];
+            if (MODE == 1) v = b[size_t(n) * N + lane] - v;
+            if ((m >> lane) & 1u) v = 0.0;
+            out[size_t(n) * N + lane] = v;
+        }
     }
 }
 
 template <int N>
 __global__ void __launch_bounds__(kWarpBlock) gsStencilWarpKernel(Grid<N> g, const Real *__restrict__ S, Real *__restrict__ u,
                                                                    const Real *__restrict__ b, const uint8_t *__restrict__ dmask, int colour,
-                                                                   int forward) {
+                                                                   int forward, int count) {
     constexpr int NST = ipow3(N), NN = N * N;
-    const int t = (blockIdx.x * kWarpBlock + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    int idx[N];
-    if (!colourNode<N>(g, t, colour, idx)) return;
-    const int n = flattenNode<N>(g, idx);
-    Real acc[N];
-    stencilWarpRow<N>(g, S, u, idx, n, lane, acc);
-    if (lane == 0) {
+    const int lane = threadIdx.x & 31, nwarps = (gridDim.x * kWarpBlock) >> 5;
+    StencilLane<N> sl; sl.init(g, lane);
+    for (int t = (blockIdx.x * kWarpBlock + threadIdx.x) >> 5; t < count; t += nwarps) {
+        int idx[N];
+        colourNode<N>(g, t, colour, idx);
+        const int n = flattenNode<N>(g, idx);
+        // the diagonal block and right-hand side do not depend on the row sums: fetch them before the reduction
         Real M[NN], tt[N];
+        unsigned mask = 0;
+        if (lane == 0) {
 #pragma unroll
-        for (int i = 0; i < NN; ++i) M[i] = S[stencilIndex<N>(n, NST / 2, i)];
+            for (int i = 0; i < NN; ++i) M[i] = S[stencilIndex<N>(n, NST / 2, i)];
 #pragma unroll
-        for (int c = 0; c < N; ++c) tt[c] = b[size_t(n) * N + c] - acc[c];
-        gsNodeUpdate<N>(tt, M, dmask[n], forward != 0, u, n);
+            for (int c = 0; c < N; ++c) tt[c] = b[size_t(n) * N + c];
+            mask = dmask[n];
+        }
+        Real acc[N];
+        stencilWarpRow<N>(sl, g.nn * N, S, u, n, lane, acc);
+        if (lane == 0) {
+#pragma unroll
+            for (int c = 0; c < N; ++c) tt[c] -= acc[c];
+            gsNodeUpdate<N>(tt, M, mask, forward != 0, u, n);
+        }
     }
 }
 

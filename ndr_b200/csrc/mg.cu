@@ -8,7 +8,7 @@
 
 namespace vfem {
 
-static const size_t kMaxCoarseBytes = size_t(16) << 30; // block factors of the coarsest level
+static const size_t kMaxCoarseBytes = size_t(32) << 30; // block factors of the coarsest level
 
 #define VFEM_CUSOLVER(call)                                                                              \
     do {                                                                                                 \
@@ -21,6 +21,8 @@ template <int N>
 MG<N>::MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels) : sim(fine) {
     dim = N;
     stream = fine->stream;
+    useGraphs = getenv("VFEM_NO_GRAPH") == nullptr;
+    if (const char *v = getenv("VFEM_GS_VARIANT")) gsVariant = atoi(v);
     int E[N];
     for (int d = 0; d < N; ++d) E[d] = fine->g.E[d];
     lv.resize(numCoarseningLevels + 1);
@@ -71,6 +73,8 @@ MG<N>::MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels) : sim(fine) 
 
 template <int N>
 MG<N>::~MG() {
+    if (pgExec) cudaGraphExecDestroy(pgExec);
+    if (captureStream) cudaStreamDestroy(captureStream);
     if (h_scal) cudaFreeHost(h_scal);
     if (cusolverHandle) cusolverDnDestroy((cusolverDnHandle_t)cusolverHandle);
     if (cublasHandle) cublasDestroy((cublasHandle_t)cublasHandle);
@@ -134,13 +138,14 @@ void MG<N>::updateElementStiffnessMatrices(bool force) {
     const size_t nd = size_t(Lc.g.nn) * N;
     const int P = Lc.g.ninc[0] * N, planes = Lc.g.n[0];
     const size_t PP = size_t(P) * P;
-    if (PP * size_t(3 * planes - 1) * sizeof(Real) > kMaxCoarseBytes)
+    if (PP * size_t(6 * planes) * sizeof(Real) > kMaxCoarseBytes)
         throw std::runtime_error("coarsest multigrid level has " + std::to_string(nd) + " dofs in planes of " + std::to_string(P) +
-                                 "; its block factorisation would need " + std::to_string(PP * size_t(3 * planes - 1) * sizeof(Real) >> 20) +
+                                 "; its block factorisation would need " + std::to_string(PP * size_t(6 * planes) * sizeof(Real) >> 20) +
                                  " MB (use more coarsening levels)");
     coarseDofs = int(nd); coarseP = P; coarsePlanes = planes;
-    { int rp = ((P + 31) / 32) * 32; coarseGroups = kTriThreads / (rp < kTriThreads ? rp : kTriThreads); if (coarseGroups < 1) coarseGroups = 1; }
-    d_blkD.alloc(PP * planes); d_blkW.alloc(PP * planes); d_blkLo.alloc(PP * size_t(planes > 1 ? planes - 1 : 1));
+    const size_t offBlocks = size_t(planes > 1 ? planes - 1 : 1);
+    d_blkD.alloc(PP * planes); d_blkW.alloc(PP * planes); d_blkLo.alloc(PP * offBlocks);
+    d_Sinv.alloc(PP * planes); d_Trm.alloc(PP * offBlocks); d_Tcm.alloc(PP * offBlocks); d_z.alloc(nd);
     d_blkD.zero(stream); d_blkLo.zero(stream);
     {
         long long tot = (long long)Lc.g.nn * NST;
@@ -161,22 +166,26 @@ void MG<N>::updateElementStiffnessMatrices(bool force) {
     VFEM_CUSOLVER(cusolverDnDpotrf_bufferSize(hnd, CUBLAS_FILL_MODE_LOWER, P, d_blkD.p, P, &lw));
     if (d_solverWork.n < size_t(lw)) d_solverWork.alloc(size_t(lw));
     if (d_info.n < size_t(planes)) d_info.alloc(size_t(planes));
-    const Real one = 1.0, mone = -1.0;
+    const Real one = 1.0, mone = -1.0, zero = 0.0;
+    auto gemm = [&](cublasOperation_t ta, cublasOperation_t tb, const Real *alpha, const Real *A, const Real *B, const Real *beta, Real *Cm) {
+        if (cublasDgemm(bh, ta, tb, P, P, P, alpha, A, P, B, P, beta, Cm, P) != CUBLAS_STATUS_SUCCESS) throw std::runtime_error("cublasDgemm failed");
+        countLaunch();
+    };
     for (int p = 0; p < planes; ++p) {
-        Real *Dp = d_blkD.p + PP * p, *Wp = d_blkW.p + PP * p;
+        Real *Dp = d_blkD.p + PP * p, *Wp = d_blkW.p + PP * p, *Sp = d_Sinv.p + PP * p;
         VFEM_CUSOLVER(cusolverDnDpotrf(hnd, CUBLAS_FILL_MODE_LOWER, P, Dp, P, d_solverWork.p, lw, d_info.p + p));
-        // W_p = C_p^{-1}: solve C_p X = I
+        // W_p = C_p^{-1} (solve C_p X = I), S_p^{-1} = W_p^T W_p
         if (cublasDtrsm(bh, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, P, P, &one, Dp, P, Wp, P) != CUBLAS_STATUS_SUCCESS)
             throw std::runtime_error("cublasDtrsm failed");
+        countLaunch(2);
+        gemm(CUBLAS_OP_T, CUBLAS_OP_N, &one, Wp, Wp, &zero, Sp);
         if (p + 1 < planes) {
-            Real *Lp = d_blkLo.p + PP * p, *Dn = d_blkD.p + PP * (p + 1);
-            // L_p = A_{p+1,p} C_p^{-T};  D_{p+1} -= L_p L_p^T
-            if (cublasDtrsm(bh, CUBLAS_SIDE_RIGHT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_T, CUBLAS_DIAG_NON_UNIT, P, P, &one, Dp, P, Lp, P) != CUBLAS_STATUS_SUCCESS)
-                throw std::runtime_error("cublasDtrsm failed");
-            if (cublasDsyrk(bh, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, P, P, &mone, Lp, P, &one, Dn, P) != CUBLAS_STATUS_SUCCESS)
-                throw std::runtime_error("cublasDsyrk failed");
+            const Real *Ap = d_blkLo.p + PP * p; // A_{p+1,p}
+            Real *Trm = d_Trm.p + PP * p, *Tcm = d_Tcm.p + PP * p, *Dn = d_blkD.p + PP * (p + 1);
+            gemm(CUBLAS_OP_N, CUBLAS_OP_N, &one, Ap, Sp, &zero, Tcm);  // T_{p+1} = A_{p+1,p} S_p^{-1}
+            gemm(CUBLAS_OP_N, CUBLAS_OP_T, &one, Sp, Ap, &zero, Trm);  // T_{p+1}^T (column-major) = T_{p+1} row-major
+            gemm(CUBLAS_OP_N, CUBLAS_OP_T, &mone, Tcm, Ap, &one, Dn);  // S_{p+1} = A_{p+1,p+1} - T_{p+1} A_{p+1,p}^T
         }
-        countLaunch(3);
     }
     std::vector<int> info(planes, 0);
     VFEM_CUDA(cudaMemcpyAsync(info.data(), d_info.p, sizeof(int) * planes, cudaMemcpyDeviceToHost, stream));
@@ -189,10 +198,19 @@ void MG<N>::updateElementStiffnessMatrices(bool force) {
 template <int N>
 void MG<N>::coarseSolve(const Real *b, Real *x) {
     const Level &Lc = lv.back();
-    const size_t smem = size_t(3 + coarseGroups) * coarseP * sizeof(Real);
-    if (smem > 48 * 1024) VFEM_CUDA(cudaFuncSetAttribute(blockTriSolveKernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    blockTriSolveKernel<N><<<1, kTriThreads, smem, stream>>>(coarseP, coarsePlanes, d_blkW.p, d_blkLo.p, b, Lc.d_dmask.p, x, coarseGroups);
-    VFEM_CHECK_LAUNCH(); countLaunch();
+    const size_t smem = size_t(2) * coarseP * sizeof(Real);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(kChainCluster); cfg.blockDim = dim3(kChainThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kChainCluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    const bool pf = coarseP <= 256 && coarseP <= 2 * kChainCluster * (kChainThreads / 32);
+    auto kern = pf ? blockTriChainKernel<N, true> : blockTriChainKernel<N, false>;
+    if (smem > 48 * 1024) VFEM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    VFEM_CUDA(cudaLaunchKernelEx(&cfg, kern, coarseP, coarsePlanes, (const Real *)d_Trm.p, (const Real *)d_Tcm.p,
+                                 (const Real *)d_Sinv.p, b, (const uint8_t *)Lc.d_dmask.p, x, d_z.p));
+    countLaunch();
 }
 
 // ---- per-level operators ------------------------------------------------------------------------------
@@ -208,7 +226,7 @@ void MG<N>::applyMode(size_t l, const Real *u, const Real *b, Real *out) {
     const unsigned blocks = unsigned((L.g.nn + kBlock - 1) / kBlock);
     if (l == 0) { sim->template applyFine<MODE>(u, b, maskOf(*this, 0), out); return; }
     (void)blocks;
-    applyStencilWarpKernel<N, MODE><<<unsigned((size_t(L.g.nn) * 32 + kWarpBlock - 1) / kWarpBlock), kWarpBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), out);
+    applyStencilWarpKernel<N, MODE><<<warpGridBlocks(L.g.nn), kWarpBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), out);
     VFEM_CHECK_LAUNCH(); countLaunch();
 }
 
@@ -224,8 +242,12 @@ void MG<N>::smoothColoured(size_t l, Real *u, const Real *b, bool forward) {
         const int colour = forward ? i : NPE - 1 - i; // MG.hh:318-320
         const int cnt = colourCount<N>(L.g, colour);
         const unsigned blocks = unsigned((cnt + kBlock - 1) / kBlock);
-        if (l == 0) gsFineKernel<N><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
-        else gsStencilWarpKernel<N><<<unsigned((size_t(cnt) * 32 + kWarpBlock - 1) / kWarpBlock), kWarpBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), colour, forward ? 1 : 0);
+        if (l == 0) {
+            if (gsVariant == 4) gsFineKernel<N, 4><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
+            else if (gsVariant == 3) gsFineKernel<N, 3><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
+            else gsFineKernel<N, 2><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
+        }
+        else gsStencilWarpKernel<N><<<warpGridBlocks(cnt), kWarpBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), colour, forward ? 1 : 0, cnt);
         VFEM_CHECK_LAUNCH(); countLaunch();
     }
 }

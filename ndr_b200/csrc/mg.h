@@ -5,9 +5,9 @@
 // Galerkin operator P^T K P as an assembled 3^N-point block stencil in SoA layout.  The reference
 // keeps a dense 24x24 Ke per coarse element (4.6 KB each) AND a block-CSC matrix per level; the
 // assembled stencil is the same linear operator, so smoothing/apply/restriction results agree to
-// roundoff.  The coarsest level is solved exactly through a block-tridiagonal Cholesky factorisation over
-// its node planes (cuSOLVER potrf + cuBLAS trsm/syrk per plane, refreshed once per density update) whose
-// solves are one kernel launch each (coarse_solve.cuh), where the reference calls CHOLMOD.
+// roundoff.  The coarsest level is solved exactly through a block-tridiagonal LDL^T factorisation over
+// its node planes (cuSOLVER potrf + cuBLAS trsm/gemm per plane, refreshed once per density update) whose
+// solves are one thread-block-cluster launch each (coarse_solve.cuh), where the reference calls CHOLMOD.
 #pragma once
 #include "sim.h"
 #include "kernels_vec.cuh"
@@ -35,8 +35,9 @@ struct MG : MGBase {
     std::vector<Level> lv;
     DevBuf<Real> d_C;               // 2^N coarsened reference stiffness matrices (MG.hh:644-648)
     // coarsest level: block-tridiagonal Cholesky over the node planes of axis 0 (coarse_solve.cuh)
-    DevBuf<Real> d_blkD, d_blkW, d_blkLo; // C_p (potrf of the diagonal blocks), W_p = C_p^{-1}, L_p
-    int coarseP = 0, coarsePlanes = 0, coarseGroups = 1;
+    DevBuf<Real> d_blkD, d_blkW, d_blkLo;   // S_p -> its Cholesky factor C_p, W_p = C_p^{-1}, A_{p+1,p}
+    DevBuf<Real> d_Sinv, d_Trm, d_Tcm, d_z; // S_p^{-1}, T_p (row- and column-major), chain scratch
+    int coarseP = 0, coarsePlanes = 0;
     int coarseDofs = 0;
     void *cublasHandle = nullptr;
     unsigned long long builtVersion = 0;
@@ -44,6 +45,19 @@ struct MG : MGBase {
     bool buildBlockStiffnessMatrices = true;       // MG.hh:746 (kept for API parity; no effect on results)
     bool buildFinestBlockStiffnessMatrix = false;  // MG.hh:750
     cudaStream_t stream = 0;
+    // The preconditioner application (one FMG / V-cycle pass: ~200 small launches) is launch-bound, so it is captured
+    // once into a CUDA graph on a private stream and replayed per PCG iteration.
+    struct PrecondKey {
+        const Real *f = nullptr; size_t steps = 0, nu = 0; bool fmg = false, sym = true; int P = 0, planes = 0;
+        bool operator==(const PrecondKey &o) const { return f == o.f && steps == o.steps && nu == o.nu && fmg == o.fmg && sym == o.sym && P == o.P && planes == o.planes; }
+    };
+    bool useGraphs = true;
+    int gsVariant = 4;              // fine-level GS: resident blocks per SM the register budget is sized for (experiment knob)
+    cudaStream_t captureStream = nullptr;
+    cudaGraphExec_t pgExec = nullptr;
+    PrecondKey pgKey;
+    unsigned long long pgLaunches = 0;
+    void precondition(const Real *f, size_t steps, size_t nu, bool fmg); // lv[0].x = M^{-1} f (MG.hh:476-479)
 
     // PCG state
     DevBuf<Real> p_x, p_r, p_d, p_Ad, p_s, p_b;

@@ -50,6 +50,42 @@ void MG<N>::solve(const Real *u, const Real *f, size_t numSteps, size_t nu, bool
     if (out != L0.x.p) VFEM_CUDA(cudaMemcpyAsync(out, L0.x.p, bytes, cudaMemcpyDeviceToDevice, stream));
 }
 
+// applyPreconditionerInv for nu > 0 (MG.hh:476-479): solve(0, f, steps, nu, true, true, null, fmg) into lv[0].x
+template <int N>
+void MG<N>::precondition(const Real *f, size_t steps, size_t nu, bool fmg) {
+    if (!useGraphs) { solve(nullptr, f, steps, nu, true, true, nullptr, fmg, lv[0].x.p); return; }
+    PrecondKey key; key.f = f; key.steps = steps; key.nu = nu; key.fmg = fmg; key.sym = symmetricGS; key.P = coarseP; key.planes = coarsePlanes;
+    if (!pgExec || !(key == pgKey)) {
+        if (pgExec) { cudaGraphExecDestroy(pgExec); pgExec = nullptr; }
+        if (!captureStream) VFEM_CUDA(cudaStreamCreateWithFlags(&captureStream, cudaStreamNonBlocking));
+        syncMasks();
+        sim->moduli();
+        VFEM_CUDA(cudaStreamSynchronize(stream));
+        const cudaStream_t saved = stream, savedSim = sim->stream;
+        const unsigned long long before = g_launchCount;
+        stream = captureStream; sim->stream = captureStream;
+        cudaGraph_t graph = nullptr;
+        VFEM_CUDA(cudaStreamBeginCapture(captureStream, cudaStreamCaptureModeRelaxed));
+        try {
+            solve(nullptr, f, steps, nu, true, true, nullptr, fmg, lv[0].x.p);
+        } catch (...) {
+            cudaStreamEndCapture(captureStream, &graph);
+            if (graph) cudaGraphDestroy(graph);
+            stream = saved; sim->stream = savedSim;
+            throw;
+        }
+        stream = saved; sim->stream = savedSim;
+        VFEM_CUDA(cudaStreamEndCapture(captureStream, &graph));
+        pgLaunches = g_launchCount - before;
+        g_launchCount = before; // nothing ran yet
+        VFEM_CUDA(cudaGraphInstantiate(&pgExec, graph, 0));
+        cudaGraphDestroy(graph);
+        pgKey = key;
+    }
+    VFEM_CUDA(cudaGraphLaunch(pgExec, stream));
+    countLaunch(pgLaunches);
+}
+
 template <int N>
 Real MG<N>::dot(const Real *a, const Real *b, size_t n) {
     dotKernel<<<reduceBlocks(n), kRedBlock, 0, stream>>>(a, b, n, rw, d_scal.p + 5);
@@ -91,7 +127,7 @@ size_t MG<N>::pcg(const Real *u, const Real *b, size_t maxIter, Real tol, const 
             VFEM_CUDA(cudaMemcpyAsync(p_s.p, r, bytes, cudaMemcpyDeviceToDevice, stream));
             s = p_s.p;
         } else {
-            solve(nullptr, r, mgIterations, nu, true, true, nullptr, fmg, lv[0].x.p);
+            precondition(r, mgIterations, nu, fmg);
             s = lv[0].x.p;
         }
         copyScalarKernel<<<1, 1, 0, stream>>>(sc + 1, sc + 0); VFEM_CHECK_LAUNCH(); countLaunch();
