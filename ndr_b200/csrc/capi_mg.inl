@@ -63,7 +63,7 @@ int vfem_mg_time_op(vfem_mg_t h, int op, size_t l, int reps, double *ms_per_call
         auto &L = mg.lv.at(l);
         auto run = [&]() {
             switch (op) {
-            case 0: mg.smoothColoured(l, L.x.p, L.b.p, true); break;
+            case 0: mg.smooth(l, L.x.p, L.b.p, true, 1); break;
             case 1: mg.computeResidual(l, L.x.p, L.b.p, L.r.p); break;
             case 2: mg.restriction(l, L.r.p, mg.lv.at(l + 1).b.p); break;
             case 3: mg.interpolate(l, mg.lv.at(l + 1).x.p, L.x.p, true); break;

@@ -6,6 +6,7 @@
 // MG.hh = VoxelFEM/MultigridSolver.hh.
 #pragma once
 #include "common.h"
+#include <cooperative_groups.h>
 
 namespace vfem {
 
@@ -136,8 +137,8 @@ struct StencilLane {
     }
 };
 
-template <int N>
-__device__ __forceinline__ void stencilWarpRow(const StencilLane<N> &sl, int ndof, const Real *__restrict__ S, const Real *__restrict__ u, int n,
+template <int N, bool LDCG = false>
+__device__ __forceinline__ void stencilWarpRow(const StencilLane<N> &sl, int ndof, const Real *__restrict__ S, const Real *u, int n,
                                                int lane, Real *acc) {
     constexpr int ROW = StencilLane<N>::ROW, J = StencilLane<N>::J;
     const Real *Sn = S + size_t(n) * N * ROW + lane;
@@ -145,7 +146,7 @@ __device__ __forceinline__ void stencilWarpRow(const StencilLane<N> &sl, int ndo
 #pragma unroll
     for (int j = 0; j < J; ++j) {
         const int a = min(max(n * N + sl.uoff[j], 0), ndof - 1);
-        uv[j] = sl.valid[j] ? u[a] : 0.0;
+        uv[j] = sl.valid[j] ? (LDCG ? __ldcg(u + a) : u[a]) : 0.0;
     }
 #pragma unroll
     for (int a = 0; a < N; ++a) {
@@ -289,6 +290,51 @@ __global__ void __launch_bounds__(kWarpBlock) gsStencilWarpKernel(Grid<N> g, con
             for (int c = 0; c < N; ++c) tt[c] -= acc[c];
             gsNodeUpdate<N>(tt, M, mask, forward != 0, u, n);
         }
+    }
+}
+
+// All colour phases of one or more Gauss-Seidel sweeps in ONE cooperative launch: phase q of the sequence visits colour
+// (forward ? q % 2^N : 2^N-1 - q % 2^N) and a grid-wide barrier separates the phases (the per-colour launches of the
+// small assembled levels are otherwise pure launch latency).  u is read with ld.global.cg: other SMs rewrite it between
+// the phases.  [q0, q1) selects the part of the sequence to run (the slab solver splits a sweep at its halo exchanges).
+template <int N>
+__global__ void __launch_bounds__(kWarpBlock) gsStencilSweepKernel(Grid<N> g, const Real *__restrict__ S, Real *u, const Real *__restrict__ b,
+                                                                    const uint8_t *__restrict__ dmask, int forward, int q0, int q1) {
+    constexpr int NST = ipow3(N), NN = N * N, NPE = 1 << N;
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    const int lane = threadIdx.x & 31, nwarps = (gridDim.x * kWarpBlock) >> 5;
+    StencilLane<N> sl; sl.init(g, lane);
+    for (int q = q0; q < q1; ++q) {
+        const int colour = forward ? (q % NPE) : (NPE - 1 - q % NPE);
+        int count = 1;
+#pragma unroll
+        for (int d = 0; d < N; ++d) { const int par = (colour >> (N - 1 - d)) & 1; count *= (g.n[d] - 1 - par) / 2 + 1; }
+        for (int t = (blockIdx.x * kWarpBlock + threadIdx.x) >> 5; t < count; t += nwarps) {
+            int idx[N];
+            colourNode<N>(g, t, colour, idx);
+            const int n = flattenNode<N>(g, idx);
+            Real M[NN], tt[N];
+            unsigned mask = 0;
+            if (lane == 0) {
+#pragma unroll
+                for (int i = 0; i < NN; ++i) M[i] = S[stencilIndex<N>(n, NST / 2, i)];
+#pragma unroll
+                for (int c = 0; c < N; ++c) tt[c] = b[size_t(n) * N + c];
+                mask = dmask[n];
+            }
+            Real acc[N];
+            stencilWarpRow<N, true>(sl, g.nn * N, S, u, n, lane, acc);
+            if (lane == 0) {
+#pragma unroll
+                for (int c = 0; c < N; ++c) tt[c] -= acc[c];
+                Real du[N];
+                if (forward) gsNodeSubst<N, true>(tt, M, mask, du); else gsNodeSubst<N, false>(tt, M, mask, du);
+#pragma unroll
+                for (int c = 0; c < N; ++c) u[size_t(n) * N + c] = __ldcg(u + size_t(n) * N + c) + du[c];
+            }
+        }
+        if (q + 1 < q1) grid.sync();
     }
 }
 

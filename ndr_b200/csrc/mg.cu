@@ -23,6 +23,7 @@ MG<N>::MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels) : sim(fine) 
     stream = fine->stream;
     useGraphs = getenv("VFEM_NO_GRAPH") == nullptr;
     if (const char *v = getenv("VFEM_GS_VARIANT")) gsVariant = atoi(v);
+    fusedSweeps = getenv("VFEM_NO_FUSED_SWEEPS") == nullptr;
     int E[N];
     for (int d = 0; d < N; ++d) E[d] = fine->g.E[d];
     lv.resize(numCoarseningLevels + 1);
@@ -250,6 +251,26 @@ void MG<N>::smoothColoured(size_t l, Real *u, const Real *b, bool forward) {
         else gsStencilWarpKernel<N><<<warpGridBlocks(cnt), kWarpBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), colour, forward ? 1 : 0, cnt);
         VFEM_CHECK_LAUNCH(); countLaunch();
     }
+}
+
+template <int N>
+void MG<N>::smooth(size_t l, Real *u, const Real *b, bool forward, size_t sweeps) {
+    if (l == 0 || !fusedSweeps || sweeps == 0) { for (size_t i = 0; i < sweeps; ++i) smoothColoured(l, u, b, forward); return; }
+    const Level &L = lv.at(l);
+    if (sweepGridBlocks == 0) {
+        int dev = 0, sms = 148, per = 1;
+        VFEM_CUDA(cudaGetDevice(&dev));
+        VFEM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        VFEM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, gsStencilSweepKernel<N>, kWarpBlock, 0));
+        sweepGridBlocks = sms * (per > 0 ? per : 1);
+    }
+    const long long need = (long long)(colourCount<N>(L.g, 0)) * 32 / kWarpBlock + 1;
+    const unsigned blocks = unsigned(need < sweepGridBlocks ? need : sweepGridBlocks);
+    Grid<N> g = L.g; const Real *S = L.S.p; const uint8_t *m = maskOf(*this, l);
+    int fw = forward ? 1 : 0, q0 = 0, q1 = int(sweeps) * NPE;
+    void *args[] = {&g, &S, &u, &b, &m, &fw, &q0, &q1};
+    VFEM_CUDA(cudaLaunchCooperativeKernel((const void *)gsStencilSweepKernel<N>, dim3(blocks), dim3(kWarpBlock), args, 0, stream));
+    countLaunch();
 }
 
 template <int N>

@@ -51,7 +51,7 @@ struct MG : MGBase {
         const Real *f = nullptr; size_t steps = 0, nu = 0; bool fmg = false, sym = true; int P = 0, planes = 0;
         bool operator==(const PrecondKey &o) const { return f == o.f && steps == o.steps && nu == o.nu && fmg == o.fmg && sym == o.sym && P == o.P && planes == o.planes; }
     };
-    bool useGraphs = true;
+    bool useGraphs = true, fusedSweeps = true;
     int gsVariant = 4;              // fine-level GS: resident blocks per SM the register budget is sized for (experiment knob)
     cudaStream_t captureStream = nullptr;
     cudaGraphExec_t pgExec = nullptr;
@@ -82,6 +82,8 @@ struct MG : MGBase {
     void computeResidual(size_t l, const Real *u, const Real *b, Real *r);             // MG.hh:401-413
     void applyKMasked(size_t l, const Real *u, Real *out);
     void smoothColoured(size_t l, Real *u, const Real *b, bool forward);               // MG.hh:336-340
+    void smooth(size_t l, Real *u, const Real *b, bool forward, size_t sweeps);        // `sweeps` x smoothColoured, fused on the assembled levels
+    int sweepGridBlocks = 0;        // co-resident blocks of gsStencilSweepKernel (cooperative launch)
     void restriction(size_t lf, const Real *vf, Real *bc);                             // MG.hh:145-180
     void interpolate(size_t lf, const Real *xc, Real *xf, bool accumulate);            // MG.hh:115-141
     void zeroOutDirichlet(size_t l, Real *u);                                          // MG.hh:364-378

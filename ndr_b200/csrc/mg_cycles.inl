@@ -7,13 +7,13 @@ void MG<N>::vcycle(size_t l, size_t nu, bool residualSystem) {
     Level &L = lv[l];
     if (l == coarsest) { coarseSolve(L.b.p, L.x.p); return; }
     enforceDirichlet(l, L.x.p, residualSystem);
-    for (size_t i = 0; i < nu; ++i) smoothColoured(l, L.x.p, L.b.p, true);
+    smooth(l, L.x.p, L.b.p, true, nu);
     computeResidual(l, L.x.p, L.b.p, L.r.p);
     restriction(l, L.r.p, lv[l + 1].b.p);
     lv[l + 1].x.zero(stream);
     vcycle(l + 1, nu, true);
     interpolate(l, lv[l + 1].x.p, L.x.p, true);
-    for (size_t i = 0; i < nu; ++i) smoothColoured(l, L.x.p, L.b.p, !symmetricGS);
+    smooth(l, L.x.p, L.b.p, !symmetricGS, nu);
 }
 
 // fullMultigrid (MG.hh:486-508)
