@@ -28,6 +28,7 @@ typedef void *vfem_tps_t;     /* TensorProductSimulator<1,..>          (VoxelFEM
 typedef void *vfem_mg_t;      /* MultigridSolver<1,..>                 (VoxelFEM.cc:94-131)  */
 typedef void *vfem_obj_t;     /* MultigridComplianceObjective          (VoxelFEM.cc:196-207) */
 typedef void *vfem_top_t;     /* TopologyOptimizationProblem           (VoxelFEM.cc:170-183) */
+typedef void *vfem_comm_t;    /* slab transport: no reference counterpart (the reference is single-node TBB)  */
 
 const char *vfem_last_error(void);
 int vfem_device_count(int *count);
@@ -100,6 +101,25 @@ typedef void (*vfem_pcg_cb)(void *ctx, size_t it, const double *x_host, const do
 int vfem_mg_pcg(vfem_mg_t h, const double *u, const double *b, size_t max_iter, double tol, vfem_pcg_cb cb, void *cb_ctx, int want_vectors,
                 size_t mg_iterations, size_t mg_smoothing_iterations, int full_multigrid, double *out, int memspace,
                 size_t *iterations, double *residual_norm);                         /* preconditionedConjugateGradient (MG.hh:679-732) */
+
+/* ---- slab decomposition along storage axis 0 (no reference counterpart) -----------------------------
+ * One rank per GPU.  A rank's simulator holds the element layers [layer_lo, layer_hi) of the global grid; node positions,
+ * boundary-condition regions and K0 are those of the global grid (TPS.hh:274-287 evaluated with global indices).
+ * Layout of a rank for L coarsening levels: its owned coarsest-level layers [c0, c1) plus ONE coarsest layer below
+ * (ranks > 0), i.e. layer_lo = (c0 - [rank > 0]) * 2^L, layer_hi = c1 * 2^L; see ndr_b200/slab.py: slab_layers().
+ * Vectors passed to the vfem_mg_* calls of a slab solver are the rank-local (numNodes_local, N) arrays. */
+int vfem_tps_create_slab(int dim, const size_t *degrees, const double *bbox_min, const double *bbox_max, const size_t *elems_global,
+                         size_t layer_lo, size_t layer_hi, vfem_tps_t *out);
+int vfem_tps_count_region_nodes(vfem_tps_t h, const double *lo, const double *hi, size_t plane_lo, size_t plane_hi, size_t *count); /* nodes of the local planes [plane_lo, plane_hi] inside a box */
+int vfem_tps_add_force_region_split(vfem_tps_t h, const double *lo, const double *hi, const double *value, size_t divisor); /* TPS.hh:381-389 with the GLOBAL node count of the region as divisor */
+int vfem_comm_nccl_unique_id(uint8_t *id128);                                       /* rank 0; broadcast the 128 bytes to the other ranks */
+int vfem_comm_create_nccl(const uint8_t *id128, int rank, int world, vfem_comm_t *out); /* collective: ncclCommInitRank on the current device */
+int vfem_comm_create_threads(int world, vfem_comm_t *out_world);                    /* `world` ranks as host threads on ONE device (single-GPU tests of the slab algorithm) */
+void vfem_comm_destroy(vfem_comm_t h);
+int vfem_mg_create_slab(vfem_tps_t tps_local, size_t num_coarsening_levels, vfem_comm_t comm, vfem_mg_t *out); /* collective */
+int vfem_mg_owned_planes(vfem_mg_t h, size_t l, size_t *first, size_t *last);       /* owned node planes (inclusive) of level l, local indices */
+int vfem_mg_exchange(vfem_mg_t h, size_t l, double *v_device, int memspace);        /* refresh the ghost planes of a level-l vector (collective) */
+int vfem_mg_dot(vfem_mg_t h, const double *a, const double *b, int memspace, double *result); /* dot product over the owned dofs of all ranks (collective) */
 
 /* ---- MultigridComplianceObjective --------------------------------------------------------------- */
 int vfem_obj_create(vfem_mg_t mg, vfem_obj_t *out);                                 /* ctor solves once (Objective.hh:78-82) */

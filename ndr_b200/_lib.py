@@ -17,7 +17,7 @@ RESIDUAL_CB = C.CFUNCTYPE(None, C.c_void_p, C.c_size_t, C.c_double)
 FILTER_CB = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t)
 
 _SCALARS = {"int": C.c_int, "size_t": C.c_size_t, "double": C.c_double, "unsigned long long": C.c_ulonglong}
-_HANDLES = {"vfem_tps_t", "vfem_mg_t", "vfem_obj_t", "vfem_top_t"}
+_HANDLES = {"vfem_tps_t", "vfem_mg_t", "vfem_obj_t", "vfem_top_t", "vfem_comm_t"}
 _CALLBACKS = {"vfem_solve_cb": SOLVE_CB, "vfem_pcg_cb": PCG_CB, "vfem_residual_cb": RESIDUAL_CB}
 
 

@@ -12,7 +12,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 SO = os.path.join(HERE, "libvfem_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-SOURCES = ["sim.cu", "mg.cu", "topopt.cu", "capi.cu"]
+SOURCES = ["sim.cu", "mg.cu", "topopt.cu", "capi.cu", "comm.cu"]
 FLAGS = (["-DVFEM_MARCH_NOBAR"] if os.environ.get("VFEM_NOBAR") else []) + ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
@@ -43,7 +43,7 @@ def build(force=False, verbose=False):
     if verbose:
         for _, log in res:
             sys.stderr.write(log)
-    cmd = [NVCC, "-shared", "-o", SO] + [o for o, _ in res] + ["-lcusolver", "-lcublas", "-Xlinker", "-rpath=/usr/local/cuda/lib64"]
+    cmd = [NVCC, "-shared", "-o", SO] + [o for o, _ in res] + ["-lcusolver", "-lcublas", "-ldl", "-Xlinker", "-rpath=/usr/local/cuda/lib64"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stderr)

@@ -10,6 +10,7 @@ thread_local std::string g_err;
 struct TpsH { int dim; std::shared_ptr<Sim<2>> s2; std::shared_ptr<Sim<3>> s3; };
 struct MgH { int dim; std::shared_ptr<MG<2>> m2; std::shared_ptr<MG<3>> m3; };
 struct ObjH { int dim; std::shared_ptr<Objective<2>> o2; std::shared_ptr<Objective<3>> o3; };
+struct CommH { std::shared_ptr<SlabComm> c; };
 struct TopH { int dim; std::shared_ptr<Problem<2>> p2; std::shared_ptr<Problem<3>> p3; };
 
 template <int N> struct Pick;
@@ -89,6 +90,26 @@ int vfem_tps_create(int dim, const size_t *degrees, const double *bbmin, const d
     *out = h;
     API_CATCH
 }
+int vfem_tps_create_slab(int dim, const size_t *degrees, const double *bbmin, const double *bbmax, const size_t *elems_global,
+                         size_t layer_lo, size_t layer_hi, vfem_tps_t *out) {
+    API_TRY
+    bool q1 = (dim == 2 || dim == 3);
+    for (int d = 0; q1 && d < dim; ++d) q1 = degrees[d] == 1;
+    if (!q1) throw std::runtime_error("No template instantiation matching degreesPerDimension!");
+    if (layer_hi <= layer_lo || layer_hi > elems_global[0]) throw std::runtime_error("invalid slab layer range");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        throw std::runtime_error("libvfem_b200: no CUDA device available (this library has no CPU fallback)");
+    size_t el[3] = {layer_hi - layer_lo, elems_global[1], dim == 3 ? elems_global[2] : 0};
+    TpsH *h = new TpsH();
+    h->dim = dim;
+    try {
+        if (dim == 2) h->s2 = std::make_shared<Sim<2>>(bbmin, bbmax, el, elems_global[0], layer_lo);
+        else h->s3 = std::make_shared<Sim<3>>(bbmin, bbmax, el, elems_global[0], layer_lo);
+    } catch (...) { delete h; throw; }
+    *out = h;
+    API_CATCH
+}
 void vfem_tps_destroy(vfem_tps_t h) { delete (TpsH *)h; }
 int vfem_tps_dim(vfem_tps_t h) { return ((TpsH *)h)->dim; }
 size_t vfem_tps_num_nodes(vfem_tps_t h) { size_t r = 0; WITH_SIM(h, r = s.numNodes();); return r; }
@@ -99,6 +120,10 @@ int vfem_tps_set_simp(vfem_tps_t h, double E_0, double E_min, double gamma) {
     API_TRY WITH_SIM(h, s.E0 = E_0; s.Emin = E_min; s.gamma = gamma; s.touchStiffness();); API_CATCH }
 int vfem_tps_get_simp(vfem_tps_t h, double *E_0, double *E_min, double *gamma) { API_TRY WITH_SIM(h, *E_0 = s.E0; *E_min = s.Emin; *gamma = s.gamma;); API_CATCH }
 int vfem_tps_add_force_region(vfem_tps_t h, const double *lo, const double *hi, const double *value) { API_TRY WITH_SIM(h, s.addForceRegion(lo, hi, value);); API_CATCH }
+int vfem_tps_add_force_region_split(vfem_tps_t h, const double *lo, const double *hi, const double *value, size_t divisor) {
+    API_TRY WITH_SIM(h, s.addForceRegion(lo, hi, value, divisor);); API_CATCH }
+int vfem_tps_count_region_nodes(vfem_tps_t h, const double *lo, const double *hi, size_t plane_lo, size_t plane_hi, size_t *count) {
+    API_TRY WITH_SIM(h, *count = s.countRegionNodes(lo, hi, plane_lo, plane_hi);); API_CATCH }
 int vfem_tps_add_dirichlet_region(vfem_tps_t h, const double *lo, const double *hi, const uint8_t *comp_mask, const double *value) {
     API_TRY WITH_SIM(h, s.addDirichletRegion(lo, hi, comp_mask, value);); API_CATCH }
 int vfem_tps_get_dirichlet(vfem_tps_t h, uint8_t *mask, double *values) {

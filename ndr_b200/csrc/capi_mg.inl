@@ -11,6 +11,33 @@ int vfem_mg_create(vfem_tps_t tps, size_t levels, vfem_mg_t *out) {
     *out = h;
     API_CATCH
 }
+// ---- slab decomposition -------------------------------------------------------------------------------------
+int vfem_comm_nccl_unique_id(uint8_t *id128) { API_TRY newNcclUniqueId(id128); API_CATCH }
+int vfem_comm_create_nccl(const uint8_t *id128, int rank, int world, vfem_comm_t *out) {
+    API_TRY CommH *h = new CommH(); try { h->c = makeNcclComm(id128, rank, world); } catch (...) { delete h; throw; } *out = h; API_CATCH }
+int vfem_comm_create_threads(int world, vfem_comm_t *out_world) {
+    API_TRY auto cs = makeThreadComms(world); for (int r = 0; r < world; ++r) { CommH *h = new CommH(); h->c = cs[r]; out_world[r] = h; } API_CATCH }
+void vfem_comm_destroy(vfem_comm_t h) { delete (CommH *)h; }
+int vfem_mg_create_slab(vfem_tps_t tps, size_t levels, vfem_comm_t comm, vfem_mg_t *out) {
+    API_TRY
+    TpsH *t = (TpsH *)tps;
+    MgH *h = new MgH(); h->dim = t->dim;
+    std::shared_ptr<SlabComm> c = comm ? ((CommH *)comm)->c : nullptr;
+    try {
+        if (t->dim == 2) h->m2 = std::make_shared<MG<2>>(t->s2, levels, c);
+        else h->m3 = std::make_shared<MG<3>>(t->s3, levels, c);
+    } catch (...) { delete h; throw; }
+    *out = h;
+    API_CATCH
+}
+int vfem_mg_owned_planes(vfem_mg_t h, size_t l, size_t *first, size_t *last) {
+    API_TRY WITH_MG(h, *first = size_t(mg.lv.at(l).g.own0); *last = size_t(mg.lv.at(l).g.own1);); API_CATCH }
+int vfem_mg_exchange(vfem_mg_t h, size_t l, double *v, int ms) {
+    API_TRY WITH_MG(h, if (ms != VFEM_DEVICE) throw std::runtime_error("vfem_mg_exchange needs a device array");
+                    mg.exchange(l, v, MG<N>::XUP | MG<N>::XDOWN);); API_CATCH }
+int vfem_mg_dot(vfem_mg_t h, const double *a, const double *b, int ms, double *result) {
+    API_TRY WITH_MG(h, size_t n = mg.levelDofs(0); Staged st(mg.stream); const double *da = st.in(a, n, ms); const double *db = st.in(b, n, ms);
+                    *result = mg.dot(da, db, n);); API_CATCH }
 void vfem_mg_destroy(vfem_mg_t h) { delete (MgH *)h; }
 size_t vfem_mg_num_levels(vfem_mg_t h) { size_t r = 0; WITH_MG(h, r = mg.numLevels();); return r; }
 size_t vfem_mg_level_nodes(vfem_mg_t h, size_t l) { size_t r = 0; WITH_MG(h, r = l < mg.lv.size() ? size_t(mg.lv[l].g.nn) : 0;); return r; }

@@ -1,6 +1,7 @@
 // ndr_b200 — transports of the slab solve (see comm.h).
 #include "comm.h"
 #include <chrono>
+#include <cstring>
 #include <dlfcn.h>
 #include <nccl.h> // types and enums only: the entry points are resolved with dlsym
 
@@ -70,7 +71,7 @@ struct NcclComm : SlabComm {
 };
 } // namespace
 
-void ncclUniqueId(uint8_t *out128) {
+void newNcclUniqueId(uint8_t *out128) {
     static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
     ncclUniqueId id;
     VFEM_NCCL(nccl().GetUniqueId(&id));
@@ -111,8 +112,8 @@ struct ThreadShared {
         std::unique_lock<std::mutex> lk(m);
         const unsigned long long gen = generation;
         if (++arrived == world) { arrived = 0; ++generation; cv.notify_all(); return; }
-        if (!cv.wait_for(lk, std::chrono::seconds(120), [&] { return generation != gen; }))
-            throw std::runtime_error("ThreadComm: a rank did not reach the collective within 120 s (ranks must make the same calls)");
+        if (!cv.wait_for(lk, std::chrono::seconds(30), [&] { return generation != gen; }))
+            throw std::runtime_error("ThreadComm: a rank did not reach the collective within 30 s (ranks must make the same calls)");
     }
 };
 

@@ -29,7 +29,7 @@ struct SlabComm {
 };
 
 std::shared_ptr<SlabComm> makeNcclComm(const uint8_t *uniqueId128, int rank, int world);
-void ncclUniqueId(uint8_t *out128);
+void newNcclUniqueId(uint8_t *out128);
 std::vector<std::shared_ptr<SlabComm>> makeThreadComms(int world);
 
 } // namespace vfem

@@ -36,8 +36,10 @@ struct Grid {
     int ninc[N];     // flat node index increments (last axis fastest)
     int einc[N];     // flat element index increments
     int nn, ne;      // totals (the largest named grid, 512x256x256, has 33.9 M nodes)
-    // Slab decomposition along storage axis 0.  A single-GPU grid has x0 = 0.
-    // All indices above are LOCAL to the slab (including one ghost node plane per interior face).
+    // Slab decomposition along storage axis 0: all indices above are LOCAL to the slab, which carries ghost
+    // node planes below own0 and above own1; [own0, own1] (inclusive) are the node planes this rank owns, i.e. updates
+    // in the smoother and counts in reductions.  A single-GPU grid owns everything (own0 = 0, own1 = n[0]-1).
+    int own0, own1;
 };
 
 template <int N>
@@ -47,6 +49,7 @@ inline Grid<N> makeGrid(const int *E) {
     for (int d = 0; d < N; ++d) { g.E[d] = E[d]; g.n[d] = E[d] + 1; nn *= g.n[d]; ne *= g.E[d]; }
     if (nn * N >= (1ll << 31)) throw std::runtime_error("grid too large for 32-bit dof indices on one device");
     g.nn = int(nn); g.ne = int(ne);
+    g.own0 = 0; g.own1 = g.n[0] - 1;
     g.ninc[N - 1] = 1; g.einc[N - 1] = 1;
     for (int d = N - 2; d >= 0; --d) { g.ninc[d] = g.ninc[d + 1] * g.n[d + 1]; g.einc[d] = g.einc[d + 1] * g.E[d + 1]; }
     return g;

@@ -26,21 +26,32 @@ __device__ __forceinline__ int flattenNode(const Grid<N> &g, const int *idx) {
     for (int d = 0; d < N; ++d) r += idx[d] * g.ninc[d];
     return r;
 }
-// thread t of colour lattice `par` (idx_d = par_d + 2*k_d); returns false when t is out of range
+// thread t of colour lattice `par` (idx_d = par_d + 2*k_d), restricted to the owned planes [own0, own1] of axis 0;
+// returns false when t is out of range
+template <int N>
+__host__ __device__ __forceinline__ int colourFirstPlane(const Grid<N> &g, int colour) {
+    const int par = (colour >> (N - 1)) & 1;
+    return g.own0 + ((g.own0 ^ par) & 1);
+}
+template <int N>
+__host__ __device__ __forceinline__ int colourPlaneCount(const Grid<N> &g, int colour) {
+    const int first = colourFirstPlane<N>(g, colour);
+    return first <= g.own1 ? (g.own1 - first) / 2 + 1 : 0;
+}
 template <int N>
 __device__ __forceinline__ bool colourNode(const Grid<N> &g, int t, int colour, int *idx) {
     int cnt[N];
 #pragma unroll
-    for (int d = 0; d < N; ++d) { int par = (colour >> (N - 1 - d)) & 1; cnt[d] = (g.n[d] - 1 - par) / 2 + 1; }
+    for (int d = 1; d < N; ++d) { int par = (colour >> (N - 1 - d)) & 1; cnt[d] = (g.n[d] - 1 - par) / 2 + 1; }
 #pragma unroll
     for (int d = N - 1; d > 0; --d) { int q = t / cnt[d]; idx[d] = ((colour >> (N - 1 - d)) & 1) + 2 * (t - q * cnt[d]); t = q; }
-    idx[0] = ((colour >> (N - 1)) & 1) + 2 * t;
-    return t < cnt[0];
+    idx[0] = colourFirstPlane<N>(g, colour) + 2 * t;
+    return t < colourPlaneCount<N>(g, colour);
 }
 template <int N>
-inline int colourCount(const Grid<N> &g, int colour) {
-    long long tot = 1;
-    for (int d = 0; d < N; ++d) { int par = (colour >> (N - 1 - d)) & 1; tot *= (g.n[d] - 1 - par) / 2 + 1; }
+__host__ __device__ inline int colourCount(const Grid<N> &g, int colour) {
+    long long tot = colourPlaneCount<N>(g, colour);
+    for (int d = 1; d < N; ++d) { int par = (colour >> (N - 1 - d)) & 1; tot *= (g.n[d] - 1 - par) / 2 + 1; }
     return int(tot);
 }
 
@@ -307,9 +318,7 @@ __global__ void __launch_bounds__(kWarpBlock) gsStencilSweepKernel(Grid<N> g, co
     StencilLane<N> sl; sl.init(g, lane);
     for (int q = q0; q < q1; ++q) {
         const int colour = forward ? (q % NPE) : (NPE - 1 - q % NPE);
-        int count = 1;
-#pragma unroll
-        for (int d = 0; d < N; ++d) { const int par = (colour >> (N - 1 - d)) & 1; count *= (g.n[d] - 1 - par) / 2 + 1; }
+        const int count = colourCount<N>(g, colour);
         for (int t = (blockIdx.x * kWarpBlock + threadIdx.x) >> 5; t < count; t += nwarps) {
             int idx[N];
             colourNode<N>(g, t, colour, idx);

@@ -18,10 +18,20 @@ static const size_t kMaxCoarseBytes = size_t(32) << 30; // block factors of the 
     } while (0)
 
 template <int N>
-MG<N>::MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels) : sim(fine) {
+MG<N>::MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels, std::shared_ptr<SlabComm> comm_) : sim(fine), comm(comm_) {
     dim = N;
+    const int Lc = int(numCoarseningLevels);
+    if (slab()) {
+        const int w = 1 << Lc, r = comm->rank, W = comm->world;
+        const int ghostLo = r > 0 ? w : 0;
+        if (fine->globalE0 % w || fine->layerLo % w || fine->g.E[0] % w || fine->g.E[0] <= ghostLo)
+            throw std::runtime_error("slab solve: the global grid and every slab boundary must be multiples of 2^numCoarseningLevels layers");
+        if ((r == 0 && fine->layerLo != 0) || (r == W - 1) != (fine->layerLo + fine->g.E[0] == fine->globalE0))
+            throw std::runtime_error("slab solve: rank 0 must hold layer 0 and the last rank the last layer");
+        useGraphs = false;
+    }
     stream = fine->stream;
-    useGraphs = getenv("VFEM_NO_GRAPH") == nullptr;
+    useGraphs = getenv("VFEM_NO_GRAPH") == nullptr && (!slab() || comm->graphSafe());
     if (const char *v = getenv("VFEM_GS_VARIANT")) gsVariant = atoi(v);
     fusedSweeps = getenv("VFEM_NO_FUSED_SWEEPS") == nullptr;
     int E[N];
@@ -31,6 +41,7 @@ MG<N>::MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels) : sim(fine) 
         Level &L = lv[l];
         if (l == 0) { L.g = fine->g; L.dmask = fine->dmask; }
         else {
+            if (slab() && l >= 2) exchangeHostMask(l - 1); // the coarsening below reads the ghost planes of the finer mask (level 0's come from node positions)
             for (int d = 0; d < N; ++d) {
                 if (E[d] % 2 == 1)
                     throw std::runtime_error("Grid size currently must be divisible by 2^numCoarseningLevels (nonuniform coarsening not yet implemented)"); // MG.hh:36-37
@@ -56,7 +67,10 @@ MG<N>::MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels) : sim(fine) 
             }
             L.S.alloc(size_t(L.g.nn) * NST * N * N);
             L.d_dval.alloc(size_t(L.g.nn) * N); L.d_dval.zero(stream);
-            L.d_dmask.upload(L.dmask, stream);
+        }
+        if (slab()) { // owned node planes of this level (see mg.h)
+            L.g.own0 = comm->rank > 0 ? (1 << (Lc - int(l))) : 0;
+            L.g.own1 = comm->rank + 1 < comm->world ? L.g.n[0] - 2 : L.g.n[0] - 1;
         }
         L.x.alloc(size_t(L.g.nn) * N); L.b.alloc(size_t(L.g.nn) * N); L.r.alloc(size_t(L.g.nn) * N);
         L.x.zero(stream); L.b.zero(stream);
@@ -69,7 +83,56 @@ MG<N>::MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels) : sim(fine) 
     VFEM_CUDA(cudaMallocHost((void **)&h_scal, 8 * sizeof(Real)));
     d_C.alloc(size_t(NPE) * KS * KS);
     d_info.alloc(1);
+    gCoarse = lv.back().g;
+    if (slab()) {
+        // global coarsest grid + its Dirichlet mask (owned rows summed over the ranks)
+        int Eg[N];
+        for (int d = 0; d < N; ++d) Eg[d] = lv.back().g.E[d];
+        Eg[0] = fine->globalE0 >> Lc;
+        gCoarse = makeGrid<N>(Eg);
+        coarsePlaneOffset = fine->layerLo >> Lc;
+        const Level &C = lv.back();
+        const size_t pn = size_t(C.g.ninc[0]);
+        std::vector<uint8_t> mg(size_t(gCoarse.nn), 0);
+        for (int p = C.g.own0; p <= C.g.own1; ++p)
+            for (size_t i = 0; i < pn; ++i) mg[size_t(coarsePlaneOffset + p) * pn + i] = C.dmask[size_t(p) * pn + i];
+        dmaskG.upload(mg, stream);
+        comm->allreduceSumBytes(dmaskG.p, dmaskG.n, stream);
+        std::vector<uint8_t> full = dmaskG.toHost(stream);
+        // the local coarsest mask (ghost planes included) is a window of the global one
+        Level &Cm = lv.back();
+        for (int p = 0; p < Cm.g.n[0]; ++p)
+            for (size_t i = 0; i < pn; ++i) Cm.dmask[size_t(p) * pn + i] = full[size_t(coarsePlaneOffset + p) * pn + i];
+        Sg.alloc(size_t(gCoarse.nn) * NST * N * N); bg.alloc(size_t(gCoarse.nn) * N); xg.alloc(size_t(gCoarse.nn) * N);
+    }
+    for (size_t l = 1; l <= numCoarseningLevels; ++l) lv[l].d_dmask.upload(lv[l].dmask, stream);
     VFEM_CUDA(cudaStreamSynchronize(stream));
+}
+
+// ghost planes of the level-l host Dirichlet mask <- the owners' planes (masks are static: done once, through the
+// device transport with the mask widened to doubles)
+template <int N>
+void MG<N>::exchangeHostMask(size_t l) {
+    Level &L = lv[l];
+    std::vector<uint8_t> &m = L.dmask;
+    const size_t pn = size_t(L.g.ninc[0]);
+    std::vector<Real> w(m.begin(), m.end());
+    DevBuf<Real> d; d.upload(w, stream);
+    const int o0 = L.g.own0, o1 = L.g.own1;
+    comm->shift(d.p + size_t(o1) * pn, o0 > 0 ? d.p + size_t(o0 - 1) * pn : d.p, d.p + size_t(o0) * pn,
+                o1 + 1 < L.g.n[0] ? d.p + size_t(o1 + 1) * pn : d.p, pn, true, true, stream);
+    d.download(w.data(), stream);
+    for (size_t i = 0; i < w.size(); ++i) m[i] = uint8_t(w[i]);
+}
+
+template <int N>
+void MG<N>::exchange(size_t l, Real *v, int dirs) {
+    if (!slab()) return;
+    const Level &L = lv[l];
+    const size_t pd = size_t(L.g.ninc[0]) * N;
+    const int o0 = L.g.own0, o1 = L.g.own1;
+    comm->shift(v + size_t(o1) * pd, o0 > 0 ? v + size_t(o0 - 1) * pd : v, v + size_t(o0) * pd, o1 + 1 < L.g.n[0] ? v + size_t(o1 + 1) * pd : v, pd,
+                (dirs & XUP) != 0, (dirs & XDOWN) != 0, stream);
 }
 
 template <int N>
@@ -134,10 +197,22 @@ void MG<N>::updateElementStiffnessMatrices(bool force) {
         galerkinStencilKernel<N><<<unsigned((tot + kBlock - 1) / kBlock), kBlock, 0, stream>>>(lv[l - 1].g, lv[l].g, lv[l - 1].S.p, lv[l].S.p);
         VFEM_CHECK_LAUNCH(); countLaunch();
     }
-    // coarsest level: block-tridiagonal Cholesky of the Dirichlet-reduced operator (coarse_solve.cuh)
-    const Level &Lc = lv[L];
-    const size_t nd = size_t(Lc.g.nn) * N;
-    const int P = Lc.g.ninc[0] * N, planes = Lc.g.n[0];
+    // coarsest level: block-tridiagonal LDL^T of the Dirichlet-reduced operator (coarse_solve.cuh).  Slab mode: the
+    // owned rows of every rank are summed into the global operator and every rank factorises it (redundantly).
+    const Grid<N> &cgrid = gCoarse;
+    const Real *cS = lv[L].S.p;
+    const uint8_t *cmask = lv[L].d_dmask.p;
+    if (slab()) {
+        const Level &Ll = lv[L];
+        const size_t rowLen = size_t(Ll.g.ninc[0]) * NST * N * N;
+        Sg.zero(stream);
+        VFEM_CUDA(cudaMemcpyAsync(Sg.p + size_t(coarsePlaneOffset + Ll.g.own0) * rowLen, Ll.S.p + size_t(Ll.g.own0) * rowLen,
+                                  size_t(Ll.g.own1 - Ll.g.own0 + 1) * rowLen * sizeof(Real), cudaMemcpyDeviceToDevice, stream));
+        comm->allreduceSum(Sg.p, Sg.n, stream);
+        cS = Sg.p; cmask = dmaskG.p;
+    }
+    const size_t nd = size_t(cgrid.nn) * N;
+    const int P = cgrid.ninc[0] * N, planes = cgrid.n[0];
     const size_t PP = size_t(P) * P;
     if (PP * size_t(6 * planes) * sizeof(Real) > kMaxCoarseBytes)
         throw std::runtime_error("coarsest multigrid level has " + std::to_string(nd) + " dofs in planes of " + std::to_string(P) +
@@ -149,8 +224,8 @@ void MG<N>::updateElementStiffnessMatrices(bool force) {
     d_Sinv.alloc(PP * planes); d_Trm.alloc(PP * offBlocks); d_Tcm.alloc(PP * offBlocks); d_z.alloc(nd);
     d_blkD.zero(stream); d_blkLo.zero(stream);
     {
-        long long tot = (long long)Lc.g.nn * NST;
-        assembleBlockTriKernel<N><<<unsigned((tot + 127) / 128), 128, 0, stream>>>(Lc.g, Lc.S.p, Lc.d_dmask.p, d_blkD.p, d_blkLo.p, P);
+        long long tot = (long long)cgrid.nn * NST;
+        assembleBlockTriKernel<N><<<unsigned((tot + 127) / 128), 128, 0, stream>>>(cgrid, cS, cmask, d_blkD.p, d_blkLo.p, P);
         VFEM_CHECK_LAUNCH(); countLaunch();
         setIdentityBlocksKernel<<<296, 256, 0, stream>>>(d_blkW.p, P, planes);
         VFEM_CHECK_LAUNCH(); countLaunch();
@@ -199,6 +274,16 @@ void MG<N>::updateElementStiffnessMatrices(bool force) {
 template <int N>
 void MG<N>::coarseSolve(const Real *b, Real *x) {
     const Level &Lc = lv.back();
+    Real *xl = x;
+    const uint8_t *cmask = Lc.d_dmask.p;
+    if (slab()) { // gather the owned planes of b into the global right-hand side; every rank solves the same system
+        const size_t pd = size_t(Lc.g.ninc[0]) * N;
+        bg.zero(stream);
+        VFEM_CUDA(cudaMemcpyAsync(bg.p + size_t(coarsePlaneOffset + Lc.g.own0) * pd, b + size_t(Lc.g.own0) * pd,
+                                  ownedDofs(lv.size() - 1) * sizeof(Real), cudaMemcpyDeviceToDevice, stream));
+        comm->allreduceSum(bg.p, bg.n, stream);
+        b = bg.p; x = xg.p; cmask = dmaskG.p;
+    }
     const size_t smem = size_t(2) * coarseP * sizeof(Real);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(kChainCluster); cfg.blockDim = dim3(kChainThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
@@ -210,8 +295,11 @@ void MG<N>::coarseSolve(const Real *b, Real *x) {
     auto kern = pf ? blockTriChainKernel<N, true> : blockTriChainKernel<N, false>;
     if (smem > 48 * 1024) VFEM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     VFEM_CUDA(cudaLaunchKernelEx(&cfg, kern, coarseP, coarsePlanes, (const Real *)d_Trm.p, (const Real *)d_Tcm.p,
-                                 (const Real *)d_Sinv.p, b, (const uint8_t *)Lc.d_dmask.p, x, d_z.p));
+                                 (const Real *)d_Sinv.p, b, cmask, x, d_z.p));
     countLaunch();
+    if (slab()) // the local window (ghost planes included) of the global solution
+        VFEM_CUDA(cudaMemcpyAsync(xl, xg.p + size_t(coarsePlaneOffset) * Lc.g.ninc[0] * N, size_t(Lc.g.nn) * N * sizeof(Real),
+                                  cudaMemcpyDeviceToDevice, stream));
 }
 
 // ---- per-level operators ------------------------------------------------------------------------------
@@ -235,6 +323,10 @@ template <int N> void MG<N>::applyK(size_t l, const Real *u, Real *out) { applyM
 template <int N> void MG<N>::computeResidual(size_t l, const Real *u, const Real *b, Real *r) { applyMode<1>(l, u, b, r); }
 template <int N> void MG<N>::applyKMasked(size_t l, const Real *u, Real *out) { applyMode<2>(l, u, nullptr, out); }
 
+// Halo traffic of a coloured sweep (slab mode): the colours whose axis-0 parity is even (the first half of the forward
+// order, MG.hh:292-294) only read odd ghost planes and vice versa, and own0 is even / own1 odd on interior faces, so a
+// sweep needs ONE one-directional plane shift after each half: even half -> first owned plane goes down, odd half ->
+// last owned plane goes up.
 template <int N>
 void MG<N>::smoothColoured(size_t l, Real *u, const Real *b, bool forward) {
     const Level &L = lv.at(l);
@@ -242,14 +334,17 @@ void MG<N>::smoothColoured(size_t l, Real *u, const Real *b, bool forward) {
     for (int i = 0; i < NPE; ++i) {
         const int colour = forward ? i : NPE - 1 - i; // MG.hh:318-320
         const int cnt = colourCount<N>(L.g, colour);
-        const unsigned blocks = unsigned((cnt + kBlock - 1) / kBlock);
-        if (l == 0) {
-            if (gsVariant == 4) gsFineKernel<N, 4><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
-            else if (gsVariant == 3) gsFineKernel<N, 3><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
-            else gsFineKernel<N, 2><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
+        if (cnt > 0) {
+            const unsigned blocks = unsigned((cnt + kBlock - 1) / kBlock);
+            if (l == 0) {
+                if (gsVariant == 4) gsFineKernel<N, 4><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
+                else if (gsVariant == 3) gsFineKernel<N, 3><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
+                else gsFineKernel<N, 2><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
+            }
+            else gsStencilWarpKernel<N><<<warpGridBlocks(cnt), kWarpBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), colour, forward ? 1 : 0, cnt);
+            VFEM_CHECK_LAUNCH(); countLaunch();
         }
-        else gsStencilWarpKernel<N><<<warpGridBlocks(cnt), kWarpBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), colour, forward ? 1 : 0, cnt);
-        VFEM_CHECK_LAUNCH(); countLaunch();
+        if (slab() && (i + 1) % (NPE / 2) == 0) exchange(l, u, (colour >> (N - 1)) & 1 ? XUP : XDOWN);
     }
 }
 
@@ -264,18 +359,30 @@ void MG<N>::smooth(size_t l, Real *u, const Real *b, bool forward, size_t sweeps
         VFEM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, gsStencilSweepKernel<N>, kWarpBlock, 0));
         sweepGridBlocks = sms * (per > 0 ? per : 1);
     }
-    const long long need = (long long)(colourCount<N>(L.g, 0)) * 32 / kWarpBlock + 1;
+    long long most = 1;
+    for (int c = 0; c < NPE; ++c) most = std::max<long long>(most, colourCount<N>(L.g, c));
+    const long long need = most * 32 / kWarpBlock + 1;
     const unsigned blocks = unsigned(need < sweepGridBlocks ? need : sweepGridBlocks);
     Grid<N> g = L.g; const Real *S = L.S.p; const uint8_t *m = maskOf(*this, l);
-    int fw = forward ? 1 : 0, q0 = 0, q1 = int(sweeps) * NPE;
-    void *args[] = {&g, &S, &u, &b, &m, &fw, &q0, &q1};
-    VFEM_CUDA(cudaLaunchCooperativeKernel((const void *)gsStencilSweepKernel<N>, dim3(blocks), dim3(kWarpBlock), args, 0, stream));
-    countLaunch();
+    int fw = forward ? 1 : 0;
+    // one launch per run of phases between two halo exchanges (the whole sequence on a single device)
+    const int total = int(sweeps) * NPE, step = slab() ? NPE / 2 : total;
+    for (int q0 = 0; q0 < total; q0 += step) {
+        int q1 = q0 + step;
+        void *args[] = {&g, &S, &u, &b, &m, &fw, &q0, &q1};
+        VFEM_CUDA(cudaLaunchCooperativeKernel((const void *)gsStencilSweepKernel<N>, dim3(blocks), dim3(kWarpBlock), args, 0, stream));
+        countLaunch();
+        if (slab()) {
+            const int colour = forward ? ((q1 - 1) % NPE) : (NPE - 1 - (q1 - 1) % NPE);
+            exchange(l, u, (colour >> (N - 1)) & 1 ? XUP : XDOWN);
+        }
+    }
 }
 
 template <int N>
 void MG<N>::restriction(size_t lf, const Real *vf, Real *bc) {
     const Level &F = lv.at(lf), &C = lv.at(lf + 1);
+    exchange(lf, const_cast<Real *>(vf), XUP); // the lowest owned coarse plane gathers from the fine ghost plane below it
     restrictKernel<N><<<(C.g.nn + kBlock - 1) / kBlock, kBlock, 0, stream>>>(F.g, C.g, vf, bc);
     VFEM_CHECK_LAUNCH(); countLaunch();
 }

@@ -11,6 +11,7 @@
 #pragma once
 #include "sim.h"
 #include "kernels_vec.cuh"
+#include "comm.h"
 #include <functional>
 
 namespace vfem {
@@ -68,7 +69,28 @@ struct MG : MGBase {
     void *cusolverHandle = nullptr;
     DevBuf<Real> d_solverWork; DevBuf<int> d_info;
 
-    MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels);
+    // ---- slab decomposition -------------------------------------------------------------------------
+    // Rank r owns the coarsest-level element layers [c0, c1) of axis 0 and, on every level l, the node planes
+    // [c0, c1) * 2^(L-l) (the last rank also the final plane).  Its local grids hold the coarsest layers [c0-1, c1)
+    // refined 2^(L-l) times, so that local fine = 2 x local coarse on every level and the transfer / Galerkin kernels
+    // run unchanged: 2^(L-l) ghost planes below the owned range (only the nearest one is ever read) and one ghost
+    // plane above it.  Vectors are "consistent" when those two ghost planes hold the neighbours' values; stencil-type
+    // operators need consistent inputs and leave ghost outputs undefined, exchange() restores consistency.
+    // The coarsest level is assembled on every rank (all-reduce of the owned rows) and solved redundantly.
+    std::shared_ptr<SlabComm> comm;  // null: single device
+    int coarsePlaneOffset = 0;       // global coarsest-level plane index of local plane 0
+    Grid<N> gCoarse;                 // global coarsest grid (== lv.back().g without a communicator)
+    DevBuf<Real> Sg, bg, xg;         // global coarsest operator / right-hand side / solution (slab mode)
+    DevBuf<uint8_t> dmaskG;
+    enum { XUP = 1, XDOWN = 2 };
+    bool slab() const { return comm && comm->world > 1; }
+    void exchange(size_t l, Real *v, int dirs);                 // halo planes of a level-l vector
+    void exchangeHostMask(size_t l);
+    void allreduce(Real *devScalars, size_t n) { if (slab()) comm->allreduceSum(devScalars, n, stream); }
+    size_t ownedOffset(size_t l) const { return size_t(lv[l].g.own0) * lv[l].g.ninc[0] * N; }
+    size_t ownedDofs(size_t l) const { return size_t(lv[l].g.own1 - lv[l].g.own0 + 1) * lv[l].g.ninc[0] * N; }
+
+    MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels, std::shared_ptr<SlabComm> comm = nullptr);
     ~MG();
     size_t numLevels() const { return lv.size(); }
     size_t levelDofs(size_t l) const { return size_t(lv.at(l).g.nn) * N; }

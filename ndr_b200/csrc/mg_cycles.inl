@@ -86,10 +86,13 @@ void MG<N>::precondition(const Real *f, size_t steps, size_t nu, bool fmg) {
     countLaunch(pgLaunches);
 }
 
+// deterministic dot product over the OWNED dofs of two level-0 vectors (+ all-reduce over the slabs), synchronous
 template <int N>
 Real MG<N>::dot(const Real *a, const Real *b, size_t n) {
+    if (slab()) { const size_t off = ownedOffset(0); a += off; b += off; n = ownedDofs(0); }
     dotKernel<<<reduceBlocks(n), kRedBlock, 0, stream>>>(a, b, n, rw, d_scal.p + 5);
     VFEM_CHECK_LAUNCH(); countLaunch();
+    allreduce(d_scal.p + 5, 1);
     VFEM_CUDA(cudaMemcpyAsync(h_scal + 5, d_scal.p + 5, sizeof(Real), cudaMemcpyDeviceToHost, stream));
     VFEM_CUDA(cudaStreamSynchronize(stream));
     return h_scal[5];
@@ -98,10 +101,14 @@ Real MG<N>::dot(const Real *a, const Real *b, size_t n) {
 // preconditionedConjugateGradient (MG.hh:679-732).  All vectors stay in HBM; per iteration the host
 // reads back one scalar (||r||^2) for the stopping test.  alpha and beta are formed on the device
 // from the fused reductions, so there is no other host round trip.
+// Slab mode: u, b, out are the rank-local arrays (ghost planes included; u must be consistent, out is); vector
+// updates and reductions run over the owned planes, each reduction is followed by a one-scalar all-reduce, and the
+// search direction gets its ghost planes refreshed before K d.
 template <int N>
 size_t MG<N>::pcg(const Real *u, const Real *b, size_t maxIter, Real tol, const PcgCb &cb, size_t mgIterations, size_t nu,
                   bool fmg, Real *out, Real *finalResidualNorm) {
-    const size_t n = levelDofs(0), bytes = n * sizeof(Real);
+    const size_t nAll = levelDofs(0), bytes = nAll * sizeof(Real);
+    const size_t off = slab() ? ownedOffset(0) : 0, n = slab() ? ownedDofs(0) : nAll;
     const int rb = reduceBlocks(n);
     syncMasks();
     Real *x = p_x.p, *r = p_r.p, *d = p_d.p, *Ad = p_Ad.p;
@@ -111,19 +118,21 @@ size_t MG<N>::pcg(const Real *u, const Real *b, size_t maxIter, Real tol, const 
     b = p_b.p;
     enforceDirichlet(0, x, false);
     updateElementStiffnessMatrices(true); // MG.hh:688-689 (+ updateBlockKs)
-    dotKernel<<<rb, kRedBlock, 0, stream>>>(b, b, n, rw, sc + 4); VFEM_CHECK_LAUNCH(); countLaunch();
+    dotKernel<<<rb, kRedBlock, 0, stream>>>(b + off, b + off, n, rw, sc + 4); VFEM_CHECK_LAUNCH(); countLaunch();
     computeResidual(0, x, b, r);
-    dotKernel<<<rb, kRedBlock, 0, stream>>>(r, r, n, rw, sc + 3); VFEM_CHECK_LAUNCH(); countLaunch();
+    dotKernel<<<rb, kRedBlock, 0, stream>>>(r + off, r + off, n, rw, sc + 3); VFEM_CHECK_LAUNCH(); countLaunch();
+    allreduce(sc + 3, 2);
     VFEM_CUDA(cudaMemcpyAsync(h_scal + 3, sc + 3, 2 * sizeof(Real), cudaMemcpyDeviceToHost, stream));
     VFEM_CUDA(cudaStreamSynchronize(stream));
     const Real bnsq = h_scal[4];
     Real rr = h_scal[3];
     size_t i = 0; // the reference leaves `i` uninitialised (MG.hh:710); 0 is the intended value
     bool first = true;
+    if (slab() && first) VFEM_CUDA(cudaMemsetAsync(d, 0, bytes, stream)); // ghost planes of d are read before they are first exchanged
     while ((i++ < maxIter) && (rr > tol * tol * bnsq)) {
         Real *s;
         if (nu == 0) { // applyPreconditionerInv returns r unchanged (MG.hh:477)
-            if (p_s.n != n) p_s.alloc(n);
+            if (p_s.n != nAll) p_s.alloc(nAll);
             VFEM_CUDA(cudaMemcpyAsync(p_s.p, r, bytes, cudaMemcpyDeviceToDevice, stream));
             s = p_s.p;
         } else {
@@ -131,17 +140,22 @@ size_t MG<N>::pcg(const Real *u, const Real *b, size_t maxIter, Real tol, const 
             s = lv[0].x.p;
         }
         copyScalarKernel<<<1, 1, 0, stream>>>(sc + 1, sc + 0); VFEM_CHECK_LAUNCH(); countLaunch();
-        maskDotKernel<N><<<rb, kRedBlock, 0, stream>>>(s, r, maskOf(*this, 0), n, rw, sc + 0); VFEM_CHECK_LAUNCH(); countLaunch();
-        updateDirectionKernel<<<rb, kRedBlock, 0, stream>>>(d, s, n, sc + 0, sc + 1, first ? 1 : 0); VFEM_CHECK_LAUNCH(); countLaunch();
+        maskDotKernel<N><<<rb, kRedBlock, 0, stream>>>(s + off, r + off, maskOf(*this, 0) + off / N, n, rw, sc + 0); VFEM_CHECK_LAUNCH(); countLaunch();
+        allreduce(sc + 0, 1);
+        updateDirectionKernel<<<rb, kRedBlock, 0, stream>>>(d + off, s + off, n, sc + 0, sc + 1, first ? 1 : 0); VFEM_CHECK_LAUNCH(); countLaunch();
         first = false;
+        exchange(0, d, XUP | XDOWN);
         applyKMasked(0, d, Ad);
-        dotKernel<<<rb, kRedBlock, 0, stream>>>(d, Ad, n, rw, sc + 2); VFEM_CHECK_LAUNCH(); countLaunch();
-        updateSolutionKernel<<<rb, kRedBlock, 0, stream>>>(x, r, d, Ad, n, sc + 0, sc + 2, rw, sc + 3); VFEM_CHECK_LAUNCH(); countLaunch();
+        dotKernel<<<rb, kRedBlock, 0, stream>>>(d + off, Ad + off, n, rw, sc + 2); VFEM_CHECK_LAUNCH(); countLaunch();
+        allreduce(sc + 2, 1);
+        updateSolutionKernel<<<rb, kRedBlock, 0, stream>>>(x + off, r + off, d + off, Ad + off, n, sc + 0, sc + 2, rw, sc + 3); VFEM_CHECK_LAUNCH(); countLaunch();
+        allreduce(sc + 3, 1);
         VFEM_CUDA(cudaMemcpyAsync(h_scal + 3, sc + 3, sizeof(Real), cudaMemcpyDeviceToHost, stream));
         VFEM_CUDA(cudaStreamSynchronize(stream));
         rr = h_scal[3];
         if (cb) cb(i, x, r, std::sqrt(rr));
     }
+    exchange(0, x, XUP | XDOWN);
     if (out != x) VFEM_CUDA(cudaMemcpyAsync(out, x, bytes, cudaMemcpyDeviceToDevice, stream));
     if (finalResidualNorm) *finalResidualNorm = std::sqrt(rr);
     return i - 1;

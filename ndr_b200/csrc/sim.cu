@@ -8,8 +8,10 @@ namespace vfem {
 unsigned long long g_launchCount = 0;
 
 template <int N>
-Sim<N>::Sim(const Real *bbmin, const Real *bbmax, const size_t *elems) {
+Sim<N>::Sim(const Real *bbmin, const Real *bbmax, const size_t *elems, size_t globalE0_, size_t layerLo_) {
     dim = N;
+    if (globalE0_ != 0 && layerLo_ + elems[0] > globalE0_) throw std::runtime_error("slab layers exceed the global grid");
+    globalE0 = int(globalE0_ ? globalE0_ : elems[0]); layerLo = int(globalE0_ ? layerLo_ : 0);
     int E[N];
     for (int d = 0; d < N; ++d) {
         if (elems[d] == 0 || elems[d] > (1u << 20)) throw std::runtime_error("invalid grid size");
@@ -18,8 +20,9 @@ Sim<N>::Sim(const Real *bbmin, const Real *bbmax, const size_t *elems) {
     g = makeGrid<N>(E);
     for (int d = 0; d < N; ++d) {
         Real len = mx[d] - mn[d];
-        spacing[d] = len / (Real(g.n[d]) - 1.0); // TPS.hh:275
-        h[d] = len / Real(g.E[d]);               // TPS.hh:287
+        const int Eg = (d == 0) ? globalE0 : g.E[d];
+        spacing[d] = len / (Real(Eg + 1) - 1.0); // TPS.hh:275
+        h[d] = len / Real(Eg);                   // TPS.hh:287
     }
     dmask.assign(g.nn, 0); dval.assign(size_t(g.nn) * N, 0.0);
     force.assign(size_t(g.nn) * N, 0.0); hasForce.assign(g.nn, 0);
@@ -90,14 +93,23 @@ static bool inRegion(const Real *p, const Real *lo, const Real *hi) { // inclusi
 }
 
 template <int N>
-void Sim<N>::addForceRegion(const Real *lo, const Real *hi, const Real *value) {
+size_t Sim<N>::countRegionNodes(const Real *lo, const Real *hi, size_t planeLo, size_t planeHi) const {
+    size_t cnt = 0; Real p[N];
+    const size_t pn = size_t(g.ninc[0]);
+    for (size_t ni = planeLo * pn; ni < (planeHi + 1) * pn && ni < size_t(g.nn); ++ni) { nodePosition(ni, p); if (inRegion<N>(p, lo, hi)) ++cnt; }
+    return cnt;
+}
+
+template <int N>
+void Sim<N>::addForceRegion(const Real *lo, const Real *hi, const Real *value, size_t divisor) {
     std::vector<size_t> hit;
     Real p[N];
     for (size_t ni = 0; ni < size_t(g.nn); ++ni) { nodePosition(ni, p); if (inRegion<N>(p, lo, hi)) hit.push_back(ni); }
-    if (hit.empty()) throw std::runtime_error("Force constraint region unmatched");
+    if (hit.empty() && divisor == 0) throw std::runtime_error("Force constraint region unmatched");
+    const Real cnt = Real(divisor ? divisor : hit.size());
     for (size_t ni : hit) {
         hasForce[ni] = 1;
-        for (int d = 0; d < N; ++d) force[ni * N + d] = value[d] / Real(hit.size()); // overwrite, TPS.hh:385-388
+        for (int d = 0; d < N; ++d) force[ni * N + d] = value[d] / cnt; // overwrite, TPS.hh:385-388
     }
 }
 
@@ -115,7 +127,7 @@ template <int N>
 void Sim<N>::addDirichletRegion(const Real *lo, const Real *hi, const uint8_t *compMask, const Real *value) {
     size_t cnt = 0; Real p[N];
     for (size_t ni = 0; ni < size_t(g.nn); ++ni) { nodePosition(ni, p); if (inRegion<N>(p, lo, hi)) { ++cnt; setDirichlet(ni, compMask, value); } }
-    if (cnt == 0) throw std::runtime_error("Dirichlet region unmatched");
+    if (cnt == 0 && globalE0 == g.E[0]) throw std::runtime_error("Dirichlet region unmatched"); // a slab may legitimately miss the region
 }
 
 template <int N>

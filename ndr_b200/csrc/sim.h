@@ -46,11 +46,21 @@ struct Sim : SimBase {
     bool EyDirty = true;
     unsigned long long densityVersion = 1; // bumped whenever K(rho) changes
 
-    Sim(const Real *bbmin, const Real *bbmax, const size_t *elems);
+    // Slab of a larger grid: this simulator holds the element layers [layerLo, layerLo + g.E[0]) of a grid
+    // with globalE0 layers along axis 0.  mn/mx/spacing/h describe the GLOBAL domain, so node positions (and with them
+    // the boundary-condition regions) and K0 are bit-identical to the undecomposed grid's.
+    int layerLo = 0, globalE0 = 0;
+
+    // elems: local element counts; globalE0 = 0 means "not a slab" (the local grid is the whole grid)
+    Sim(const Real *bbmin, const Real *bbmax, const size_t *elems, size_t globalE0 = 0, size_t layerLo = 0);
 
     // TPS.hh:274-279
     void nodePosition(size_t ni, Real *p) const {
-        for (int d = N - 1; d >= 0; --d) { size_t i = ni % size_t(g.n[d]); ni /= size_t(g.n[d]); p[d] = mn[d] + Real(i) * spacing[d]; }
+        for (int d = N - 1; d >= 0; --d) {
+            size_t i = ni % size_t(g.n[d]); ni /= size_t(g.n[d]);
+            if (d == 0) i += size_t(layerLo);
+            p[d] = mn[d] + Real(i) * spacing[d];
+        }
     }
     size_t numNodes() const { return size_t(g.nn); }
     size_t numElements() const { return size_t(g.ne); }
@@ -61,7 +71,9 @@ struct Sim : SimBase {
     void touchStiffness() { EyDirty = true; ++densityVersion; }
 
     // boundary conditions (TPS.hh:358-409, Node::setDirichlet TPS.hh:49-63)
-    void addForceRegion(const Real *lo, const Real *hi, const Real *value);
+    // divisor: number of nodes the force is split over; 0 = the nodes of this grid inside the region (TPS.hh:385-388)
+    void addForceRegion(const Real *lo, const Real *hi, const Real *value, size_t divisor = 0);
+    size_t countRegionNodes(const Real *lo, const Real *hi, size_t planeLo, size_t planeHi) const; // local planes [planeLo, planeHi]
     void addDirichletRegion(const Real *lo, const Real *hi, const uint8_t *compMask, const Real *value);
     void setDirichlet(size_t ni, const uint8_t *compMask, const Real *value);
     void buildLoadVectorHost(Real *f) const;  // TPS.hh:893-901

@@ -1,0 +1,152 @@
+"""Slab-decomposed solve on ONE GPU: W ranks as W host threads sharing the device (ThreadComm, csrc/comm.cu).
+Every rank's local results are compared with the CPU oracle's solution of the UNDECOMPOSED grid."""
+import threading
+
+import numpy as np
+import pytest
+
+from conftest import MATERIAL, bc_path
+
+pytestmark = pytest.mark.gpu
+
+DOM, BC = [2.0, 1.0, 1.0], "3d/cantilever_flexion.bc"
+
+
+def rel(a, b):
+    return float(np.max(np.abs(np.asarray(a) - np.asarray(b))) / max(np.max(np.abs(b)), 1e-300))
+
+
+def oracle_problem(O, grid, levels):
+    o = O.OracleSim([0, 0, 0], DOM, grid)
+    o.read_material(MATERIAL)
+    rho = np.random.default_rng(88).uniform(0, 1, o.ne)
+    o.set_densities(rho)
+    o.apply_bc_file(bc_path(BC))
+    o.set_simp(1.0, 1e-4, 3.0)
+    o.mg_create(levels)
+    return o, rho
+
+
+def run_ranks(world, body):
+    """runs body(rank) on `world` threads; re-raises the first failure"""
+    errs = [None] * world
+
+    def wrap(r):
+        try:
+            body(r)
+        except BaseException as e:  # noqa: BLE001
+            errs[r] = e
+    ts = [threading.Thread(target=wrap, args=(r,)) for r in range(world)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    bad = [(r, e) for r, e in enumerate(errs) if e is not None]
+    if bad:
+        # a rank that fails leaves the others waiting at a collective until they time out: report the root cause first
+        bad.sort(key=lambda re: "did not reach the collective" in str(re[1]))
+        raise RuntimeError("; ".join("rank %d: %s: %s" % (r, type(e).__name__, e) for r, e in bad)) from bad[0][1]
+
+
+def make_rank(grid, levels, rank, world, comms, hs, rho):
+    from ndr_b200.slab import SlabSolver
+    s = SlabSolver(grid, np.zeros(3), np.array(DOM), levels, rank, world, comms[rank], hs.bind(rank), MATERIAL)
+    s.tps.setElementDensities(np.ascontiguousarray(rho[s.layout.elem_slice()]))
+    s.apply_bc_file(bc_path(BC))
+    s.tps.E_0, s.tps.E_min, s.tps.gamma = 1.0, 1e-4, 3.0
+    return s
+
+
+@pytest.mark.parametrize("grid,levels,world", [([32, 16, 16], 2, 2), ([32, 16, 16], 2, 4), ([48, 16, 16], 3, 3), ([32, 8, 8], 1, 5)])
+def test_slab_setup_and_apply(oracle_mod, grid, levels, world):
+    """local load vector / Dirichlet mask = windows of the global ones; K u on the owned planes = global K u"""
+    from ndr_b200.slab import ThreadHostSum, make_thread_comms
+    o, rho = oracle_problem(oracle_mod, grid, levels)
+    f, dm = o.load_vector(), o.mg_level_dmask(0).astype(bool)
+    u = np.random.default_rng(89).standard_normal((o.nn, 3))
+    Ku = o.apply_k(u)
+    comms, hs = make_thread_comms(world), ThreadHostSum(world)
+
+    def body(r):
+        s = make_rank(grid, levels, r, world, comms, hs, rho)
+        L = s.layout
+        np.testing.assert_array_equal(s.tps.buildLoadVector(), f[L.node_slice()])
+        np.testing.assert_array_equal(s.tps.dirichletMask, dm[L.node_slice()])
+        out = s.tps.applyK(np.ascontiguousarray(u[L.node_slice()]))
+        assert rel(out[L.owned_node_rows()], Ku[L.owned_global_node_rows()]) < 1e-13
+    run_ranks(world, body)
+
+
+@pytest.mark.parametrize("grid,levels,world", [([32, 16, 16], 2, 2), ([32, 16, 16], 2, 4), ([48, 16, 16], 3, 3)])
+def test_slab_hierarchy_and_smoother(oracle_mod, grid, levels, world):
+    """per-level Dirichlet masks, one coloured GS sweep and the residual on every level against the oracle's"""
+    from ndr_b200.slab import ThreadHostSum, make_thread_comms
+    o, rho = oracle_problem(oracle_mod, grid, levels)
+    o.mg_update_stiffness()
+    rng = np.random.default_rng(5)
+    ref = {}
+    for l in range(levels):
+        nn = o.mg_level_nodes(l)
+        u, b = rng.standard_normal((nn, 3)), rng.standard_normal((nn, 3))
+        u = o.mg_zero_dirichlet(l, u)
+        ref[l] = (u, b, o.mg_smooth(l, u.copy(), b, True), o.mg_smooth(l, u.copy(), b, False), o.mg_residual(l, u, b), o.mg_level_dmask(l).astype(bool))
+    comms, hs = make_thread_comms(world), ThreadHostSum(world)
+
+    def body(r):
+        import ctypes as C
+        from ndr_b200._lib import check, lib
+        s = make_rank(grid, levels, r, world, comms, hs, rho)
+        mg = s.multigrid()
+        pn = s.layout.plane_nodes
+        for l in range(levels):
+            u, b, uf, ub, res, dm = ref[l]
+            w = 1 << l
+            first, last = C.c_size_t(), C.c_size_t()
+            check(lib().vfem_mg_owned_planes(mg._h, l, C.byref(first), C.byref(last)))
+            pnl = (grid[1] // w + 1) * (grid[2] // w + 1)
+            p0 = s.layout.layer_lo // w
+            nloc = mg.getSimulator(l).numNodes()
+            win = slice(p0 * pnl, p0 * pnl + nloc)
+            own_l = slice(first.value * pnl, (last.value + 1) * pnl)
+            own_g = slice((p0 + first.value) * pnl, (p0 + last.value + 1) * pnl)
+            if l > 0:
+                np.testing.assert_array_equal(mg.getSimulator(l).dirichletMask[own_l], dm[own_g])
+            for fwd, want in ((True, uf), (False, ub)):
+                got = mg.smoothingMulticoloredGS(l, np.ascontiguousarray(u[win]), np.ascontiguousarray(b[win]), fwd)
+                assert rel(got[own_l], want[own_g]) < 1e-12, (l, fwd)
+            got = mg.computeResidual(l, np.ascontiguousarray(u[win]), np.ascontiguousarray(b[win]))
+            assert rel(got[own_l], res[own_g]) < 1e-12, l
+    run_ranks(world, body)
+
+
+@pytest.mark.parametrize("grid,levels,world", [([32, 16, 16], 2, 2), ([32, 16, 16], 2, 4), ([48, 16, 16], 3, 3), ([64, 16, 16], 3, 8)])
+def test_slab_mg_pcg(oracle_mod, grid, levels, world):
+    """MG-PCG (FMG preconditioner, 2 sweeps): fixed-iteration iterates and the converged solution against the oracle"""
+    from ndr_b200.slab import ThreadHostSum, make_thread_comms
+    o, rho = oracle_problem(oracle_mod, grid, levels)
+    f = o.load_vector()
+    want = {}
+    for its, tol in ((3, 1e-30), (100, 1e-10)):
+        want[its] = o.mg_pcg(np.zeros_like(f), f, its, tol, 1, 2, True)
+    comms, hs = make_thread_comms(world), ThreadHostSum(world)
+
+    def body(r):
+        s = make_rank(grid, levels, r, world, comms, hs, rho)
+        L = s.layout
+        mg = s.multigrid()
+        fl = s.tps.buildLoadVector()
+        for its, tol in ((3, 1e-30), (100, 1e-10)):
+            uo, no, _ = want[its]
+            u, n, _ = mg.preconditionedConjugateGradient(np.zeros_like(fl), fl, its, tol, mgIterations=1, mgSmoothingIterations=2,
+                                                         fullMultigrid=True, return_info=True)
+            assert n == no
+            scale = np.max(np.abs(uo))
+            # owned planes AND the ghost planes next to them (the returned field is consistent)
+            lo, hi = max(L.own0 - 1, 0), min(L.own1 + 1, L.local_planes - 1)
+            rows = slice(lo * L.plane_nodes, (hi + 1) * L.plane_nodes)
+            grow = slice((L.layer_lo + lo) * L.plane_nodes, (L.layer_lo + hi + 1) * L.plane_nodes)
+            assert np.max(np.abs(u[rows] - uo[grow])) / scale < 1e-10, (its, r)
+        # compliance 1/2 f.u over the owned dofs of all ranks
+        J = 0.5 * s.dot(fl, u)
+        assert abs(J - 0.5 * float(np.sum(f * want[100][0]))) < 1e-10 * abs(J)
+    run_ranks(world, body)
