@@ -8,7 +8,8 @@ A step = one matrix-free K(rho) u over the grid (3-D cantilever 128x64x64 per GP
   solve   : ms per MG-PCG solve (reference production settings: FMG preconditioner, 2 smoothing sweeps, tol 1e-4)
   roofline: algorithmic bytes 8*(2*N*nn + ne) per apply / CUDA-event time, against MEASURED_PEAKS.json hbm_gbs
   cpu_baseline: the CPU restatement of the reference algorithm (oracle/, OpenMP) on this box's host cores
-N > 1 (torchrun): slabs along storage axis 0, one ghost node plane exchanged per apply over NCCL; weak scaling.
+N > 1 (torchrun): slabs along storage axis 0 (ndr_b200/slab.py); the K-apply step exchanges one node plane per interior
+face (ncclSend/ncclRecv issued by the C++ solver on its stream) and `solve` is the slab-decomposed MG-PCG; weak scaling.
 `--impl reference` times the CPU restatement (the reference itself cannot be built here: no Eigen/TBB/SuiteSparse).
 """
 import argparse
@@ -130,12 +131,19 @@ def reference_arm(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def layer_densities(layer_lo, layer_hi, plane_elems):
+    """synthetic densities of global element layers [layer_lo, layer_hi): one seeded stream per layer, so that the ghost
+    layers of neighbouring ranks hold identical values whatever the decomposition"""
+    return np.concatenate([np.random.default_rng([88, k]).uniform(0, 1, plane_elems) for k in range(layer_lo, layer_hi)])
+
+
 def our_arm(args):
     import torch
     import torch.distributed as dist
     from ndr_b200 import _lib
-    from ndr_b200.slab import SlabKApply, partition
+    from ndr_b200 import slab as S
     import ndr_b200.pyVoxelFEM as V
+    from ndr_b200.voxelfem import _dev_ptr
 
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
     if not torch.cuda.is_available():
@@ -146,31 +154,46 @@ def our_arm(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     W, K = args.warmup, args.steps
     hbm_peak, peak_src = measured_peaks()
+    L = _lib.lib()
 
     # ---- workload: weak scaling, one 128x64x64 block of element layers per GPU, slabs along axis 0 ----
     gE = [GRID[0] * world, GRID[1], GRID[2]]
     bbmin, bbmax = np.zeros(3), np.array([DOMAIN[0] * world, DOMAIN[1], DOMAIN[2]])
-    e0, e1 = partition(gE[0], world, rank)
-    lo, hi = e0 - (1 if rank > 0 else 0), e1 + (1 if rank < world - 1 else 0)
-    rho_local = np.random.default_rng(88 + rank).uniform(0, 1, (hi - lo) * gE[1] * gE[2])
-    slab = SlabKApply(gE, bbmin, bbmax, rank, world, MATERIAL, rho_local)
-    slab.tps.E_0, slab.tps.E_min, slab.tps.gamma = 1.0, 1e-4, 3.0
-    nn_l, ne_l = slab.tps.numNodes(), slab.tps.numElements()
+    if world == 1:
+        tps = V.TensorProductSimulator([1, 1, 1], [bbmin, bbmax], gE)
+        tps.readMaterial(MATERIAL)
+        tps.setElementDensities(np.random.default_rng(88).uniform(0, 1, tps.numElements()))
+        tps.applyDisplacementsAndLoadsFromFile(BC)
+        tps.E_0, tps.E_min, tps.gamma = 1.0, 1e-4, 3.0
+        mg = tps.multigridSolver(args.levels)
+        halo_bytes = 0
+        exchange = lambda u: None
+    else:
+        comm = S.make_nccl_comm(dist, rank, world)
+        sl = S.SlabSolver(gE, bbmin, bbmax, args.levels, rank, world, comm, S.dist_host_sum(dist, torch.device("cuda", local)), MATERIAL)
+        tps, lay = sl.tps, sl.layout
+        tps.setElementDensities(layer_densities(lay.layer_lo, lay.layer_hi, lay.plane_elems))
+        sl.apply_bc_file(BC)
+        tps.E_0, tps.E_min, tps.gamma = 1.0, 1e-4, 3.0
+        mg = sl.multigrid()
+        halo_bytes = lay.plane_nodes * 24
+        exchange = lambda u: _lib.check(L.vfem_mg_exchange(mg._h, 0, _dev_ptr(u, u.numel()), 1))
+    nn_l, ne_l = tps.numNodes(), tps.numElements()
     nn_global = (gE[0] + 1) * (gE[1] + 1) * (gE[2] + 1)
     set_bytes = algorithmic_bytes(nn_l, ne_l)
     nsets = max(2, int(np.ceil(2.5 * L2_BYTES / (16 * 3 * nn_l))))  # ring of u/Ku pairs larger than L2
     gen = torch.Generator(device="cuda"); gen.manual_seed(89 + rank)
     us = [torch.randn(nn_l, 3, dtype=torch.float64, device="cuda", generator=gen) for _ in range(nsets)]
     outs = [torch.empty(nn_l, 3, dtype=torch.float64, device="cuda") for _ in range(nsets)]
-    L = _lib.lib()
 
     def sync_all():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step(k):
-        slab.apply(us[k % nsets], outs[k % nsets], dist if world > 1 else None)
+    def step(k):  # halo exchange of u (one node plane per interior face over NVLink) + the local matrix-free apply
+        exchange(us[k % nsets])
+        tps.applyK(us[k % nsets], out=outs[k % nsets])
 
     for k in range(W):
         step(k)
@@ -190,7 +213,7 @@ def our_arm(args):
     t_end = time.perf_counter() + 0.6
     while time.perf_counter() < t_end:
         for k in range(50):
-            slab.tps.applyK(us[k % nsets], out=outs[k % nsets])
+            tps.applyK(us[k % nsets], out=outs[k % nsets])
         torch.cuda.synchronize()
     clocks = sampler.stop()
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
@@ -203,16 +226,21 @@ def our_arm(args):
     torch.cuda.synchronize()
     ev0.record()
     for k in range(K):
-        slab.tps.applyK(us[k % nsets], out=outs[k % nsets])
+        tps.applyK(us[k % nsets], out=outs[k % nsets])
     ev1.record(); torch.cuda.synchronize()
     kms = ev0.elapsed_time(ev1) / K
     achieved = set_bytes / (kms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "applyFineKernel<3,0> (matrix-free K(rho)u)", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": set_bytes,
-                "kernel_ms": kms, "gdof_per_s_per_gpu": 3.0 * nn_l / (kms * 1e-3) / 1e9}
+    roofline = {"bound": "hbm", "kernel": "applyMarchKernel<0,...> (matrix-free K(rho)u, element-marching Walsh-Hadamard form)", "achieved": achieved,
+                "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": set_bytes, "kernel_ms": kms, "gdof_per_s_per_gpu": 3.0 * nn_l / (kms * 1e-3) / 1e9}
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
-        roofline["traffic"] = json.load(open(tp)).get("apply_fine_dram_bytes_per_launch")
+        roofline["traffic"] = json.load(open(tp)).get("apply_march_dram_bytes_per_launch")
+
+    # ---- MG-PCG solve over all ranks (collective: every rank takes part) ----
+    solve = None
+    if not args.no_solve:
+        solve = time_solve(V, torch, args, tps, mg, world, dist)
 
     if rank != 0:
         if world > 1:
@@ -224,26 +252,22 @@ def our_arm(args):
     oh = torch.empty(nn_l, 3, dtype=torch.float64).pin_memory().numpy()
     ke = max(3, min(K, 20))
     for _ in range(2):
-        slab.tps.applyK(uh, out=oh)
+        tps.applyK(uh, out=oh)
     torch.cuda.synchronize(); ev0.record()
     for _ in range(ke):
-        slab.tps.applyK(uh, out=oh)
+        tps.applyK(uh, out=oh)
     ev1.record(); torch.cuda.synchronize()
     e2e_ms = ev0.elapsed_time(ev1) / ke
     e2e = {"value": 3.0 * nn_l * world / (e2e_ms * 1e-3) / 1e9, "unit": "GDOF/s", "h2d_bytes_per_step": int(uh.nbytes), "d2h_bytes_per_step": int(oh.nbytes),
            "ms_per_step": e2e_ms, "call": "pyVoxelFEM TensorProductSimulator.applyK(numpy) -> vfem_tps_apply_k(VFEM_HOST), rank 0's slab"}
 
-    # ---- MG-PCG solve (single GPU, full 128x64x64 cantilever with its boundary conditions) ----
-    solve = None
-    if not args.no_solve:
-        solve = time_solve(V, torch, args)
     cpu = run_cpu_kapply(args.cpu_seconds, solve=not args.no_solve) if world == 1 and not args.no_cpu else None
     line = {"metric": "k_apply_gdof_per_s", "value": value, "unit": "GDOF/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "3D cantilever %dx%dx%d Q1 hex (128x64x64 element layers per GPU, slabs along axis 0), matrix-free K(rho)u, "
                                    "seed-88 uniform(0,1) densities, E_min=1e-4, p=3" % tuple(gE),
                        "dofs": 3 * nn_global, "l2": "ring of %d u/Ku buffer pairs (%.0f MB) > 126 MB L2" % (nsets, nsets * 48 * nn_l / 1e6),
-                       "halo": "none" if world == 1 else "1 node plane (%d B) per interior face per apply, torch.distributed NCCL send/recv" % (slab.layout.plane_nodes * 24)},
+                       "halo": "none" if world == 1 else "1 node plane (%d B) per interior face per apply, ncclSend/ncclRecv on the solver stream" % halo_bytes},
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline}
     if solve:
         line["solve"] = solve
@@ -254,36 +278,41 @@ def our_arm(args):
         dist.barrier(); dist.destroy_process_group()
 
 
-def time_solve(V, torch, args, reps=5):
-    g = V.TensorProductSimulator([1, 1, 1], [np.zeros(3), np.array(DOMAIN)], GRID)
-    g.readMaterial(MATERIAL)
-    rho = np.random.default_rng(88).uniform(0, 1, g.numElements())
-    g.setElementDensities(rho)
-    g.applyDisplacementsAndLoadsFromFile(BC)
-    g.E_0, g.E_min, g.gamma = 1.0, 1e-4, 3.0
-    mg = g.multigridSolver(args.levels)
+def time_solve(V, torch, args, g, mg, world, dist, reps=5):
+    """ms per MG-PCG solve of the bench grid (all ranks), reference production settings (fem.py:66-70)."""
     f = torch.from_numpy(g.buildLoadVector()).cuda()
     u0 = torch.zeros_like(f); out = torch.empty_like(f)
     kw = dict(mgIterations=1, mgSmoothingIterations=2, fullMultigrid=True, out=out)
     mg.preconditionedConjugateGradient(u0, f, 100, 1e-4, **kw)
     torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     for _ in range(reps):
         mg.preconditionedConjugateGradient(u0, f, 100, 1e-4, **kw)
     ev1.record(); torch.cuda.synchronize()
-    ms = ev0.elapsed_time(ev1) / reps
+    t = torch.tensor([ev0.elapsed_time(ev1) / reps], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
     its = mg.lastIterations
-    # e2e: densities (host) in -> solve -> compliance + per-voxel gradient (host) out, as VoxelFEMFunction.forward does (fem.py:109-129)
-    obj = V.MultigridComplianceObjective(mg)
-    obj.tol, obj.zeroInit = 1e-4, True
-    t0 = time.perf_counter()
-    for _ in range(3):
-        obj.updateCache(rho); J = obj.compliance(); gr = obj.gradient()
-    e2e_ms = (time.perf_counter() - t0) / 3 * 1e3
-    return {"ms_per_solve": ms, "iterations": int(its), "dofs": 3 * g.numNodes(), "mdof_per_s": 3 * g.numNodes() / ms / 1e3,
-            "protocol": "zero initial guess, tol 1e-4, %d coarsening levels, FMG preconditioner, 2 GS sweeps, operator refresh included" % args.levels,
-            "e2e_ms_densities_to_gradient": e2e_ms, "compliance": float(J), "residual": mg.lastResidualNorm}
+    nn_global = (GRID[0] * world + 1) * (GRID[1] + 1) * (GRID[2] + 1)
+    res = {"ms_per_solve": ms, "iterations": int(its), "dofs": 3 * nn_global, "mdof_per_s": 3 * nn_global / ms / 1e3, "n_gpus": world,
+           "protocol": "zero initial guess, tol 1e-4, %d coarsening levels, FMG preconditioner, 2 GS sweeps, operator refresh included" % args.levels,
+           "residual": mg.lastResidualNorm}
+    if world == 1:
+        # e2e: densities (host) in -> solve -> compliance + per-voxel gradient (host) out, as VoxelFEMFunction.forward does (fem.py:109-129)
+        rho = g.getDensities()
+        obj = V.MultigridComplianceObjective(mg)
+        obj.tol, obj.zeroInit = 1e-4, True
+        obj.updateCache(rho); obj.compliance(); obj.gradient()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            obj.updateCache(rho); J = obj.compliance(); gr = obj.gradient()
+        res["e2e_ms_densities_to_gradient"] = (time.perf_counter() - t0) / 3 * 1e3
+        res["compliance"] = float(J)
+    return res
 
 
 def main():

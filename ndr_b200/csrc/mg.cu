@@ -85,6 +85,7 @@ MG<N>::MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels, std::shared_
     d_info.alloc(1);
     gCoarse = lv.back().g;
     if (slab()) {
+        sim->computeLo = lv[0].g.own0 > 1 ? lv[0].g.own0 - 1 : 0;
         // global coarsest grid + its Dirichlet mask (owned rows summed over the ranks)
         int Eg[N];
         for (int d = 0; d < N; ++d) Eg[d] = lv.back().g.E[d];

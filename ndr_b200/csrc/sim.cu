@@ -200,10 +200,30 @@ template <int N>
 template <int MODE>
 void Sim<N>::applyFine(const Real *u, const Real *b, const uint8_t *mask, Real *out) {
     const Real *Ey = moduli();
+    // slab solver: the element layers below computeLo only feed ghost planes nobody reads - skip them by viewing the
+    // grid from layer computeLo on (the kernels do not depend on the absolute plane index)
+    Grid<N> gv = g;
+    if (computeLo > 0) {
+        int E[N];
+        for (int d = 0; d < N; ++d) E[d] = g.E[d];
+        E[0] -= computeLo;
+        gv = makeGrid<N>(E);
+        const size_t po = size_t(computeLo) * g.ninc[0];
+        u += po * N; out += po * N; Ey += size_t(computeLo) * g.einc[0];
+        if (b) b += po * N;
+        if (mask) mask += po;
+        if (N == 3 && computeLoPlanned != computeLo) {
+            int dev = 0, sms = 148;
+            if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            marchPlanView = planMarch(reinterpret_cast<const Grid<3> &>(gv), sms > 0 ? sms : 148);
+            computeLoPlanned = computeLo;
+        }
+    }
     if (useMarch())
-        launchApplyMarch<MODE>(reinterpret_cast<const Grid<3> &>(g), Khat, khatStructure == 2 && applyVariant != 2, marchPlan, Ey, u, b, mask, out, stream);
+        launchApplyMarch<MODE>(reinterpret_cast<const Grid<3> &>(gv), Khat, khatStructure == 2 && applyVariant != 2, computeLo > 0 ? marchPlanView : marchPlan,
+                               Ey, u, b, mask, out, stream);
     else
-        applyFineKernel<N, MODE><<<(g.nn + kBlock - 1) / kBlock, kBlock, 0, stream>>>(g, K0, Ey, u, b, mask, out);
+        applyFineKernel<N, MODE><<<(gv.nn + kBlock - 1) / kBlock, kBlock, 0, stream>>>(gv, K0, Ey, u, b, mask, out);
     VFEM_CHECK_LAUNCH(); countLaunch();
 }
 

@@ -50,6 +50,8 @@ struct Sim : SimBase {
     // with globalE0 layers along axis 0.  mn/mx/spacing/h describe the GLOBAL domain, so node positions (and with them
     // the boundary-condition regions) and K0 are bit-identical to the undecomposed grid's.
     int layerLo = 0, globalE0 = 0;
+    int computeLo = 0, computeLoPlanned = -1; // first local element layer K u is evaluated on (set by the slab solver)
+    MarchPlan marchPlanView;
 
     // elems: local element counts; globalE0 = 0 means "not a slab" (the local grid is the whole grid)
     Sim(const Real *bbmin, const Real *bbmax, const size_t *elems, size_t globalE0 = 0, size_t layerLo = 0);

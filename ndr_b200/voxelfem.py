@@ -109,7 +109,10 @@ class TensorProductSimulator:
 
     def __del__(self):
         if getattr(self, "_h", None) and lib is not None:  # `lib` is None during interpreter shutdown
-            lib().vfem_tps_destroy(self._h)
+            try:
+                lib().vfem_tps_destroy(self._h)
+            except Exception:  # interpreter shutdown
+                pass
             self._h = None
 
     # --- sizes / indexing (NDVector order: first axis slowest) ---

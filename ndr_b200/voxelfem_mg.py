@@ -42,7 +42,10 @@ class MultigridSolver:
 
     def __del__(self):
         if getattr(self, "_h", None) and lib is not None:
-            lib().vfem_mg_destroy(self._h)
+            try:
+                lib().vfem_mg_destroy(self._h)
+            except Exception:  # interpreter shutdown
+                pass
             self._h = None
 
     def numLevels(self):
@@ -188,7 +191,10 @@ class MultigridComplianceObjective:
 
     def __del__(self):
         if getattr(self, "_h", None) and lib is not None:
-            lib().vfem_obj_destroy(self._h)
+            try:
+                lib().vfem_obj_destroy(self._h)
+            except Exception:  # interpreter shutdown
+                pass
             object.__setattr__(self, "_h", None)
 
     def _params(self):

@@ -109,7 +109,10 @@ class TopologyOptimizationProblem:
 
     def __del__(self):
         if getattr(self, "_h", None) and lib is not None:
-            lib().vfem_top_destroy(self._h)
+            try:
+                lib().vfem_top_destroy(self._h)
+            except Exception:  # interpreter shutdown
+                pass
             self._h = None
 
     objective = property(lambda s: s._objective)
