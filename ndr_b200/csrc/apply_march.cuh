@@ -350,14 +350,18 @@ inline int computeKhat(const Real *K0 /*24x24*/, KhatParam &kh) {
     return structure;
 }
 
+constexpr int kMarchShapes = 11;
 struct MarchPlan { int cfg = 0, XC = 2; dim3 grid; };
 
-// picks the tile shape with the fewest thread-steps, then the chunk length that fills the SMs (1 CTA / SM)
+// Picks tile shape and chunk length from a measured cost model: a CTA advances one plane per step, and a step takes
+// stepUs[shape] on B200 whatever the chunk length (the march is latency-bound: profiles/r01d_march_shape_sweep.txt), so
+// cost = waves * (steps per chunk + pipeline fill) * stepUs, with waves = CTAs / (SMs * resident CTAs per SM).
 inline MarchPlan planMarch(const Grid<3> &g, int numSMs) {
-    static const int shapes[7][2] = {{8, 64}, {16, 32}, {15, 33}, {7, 65}, {6, 64}, {4, 64}, {8, 32}};
+    static const int shapes[kMarchShapes][2] = {{8, 64}, {16, 32}, {15, 33}, {7, 65}, {6, 64}, {4, 64}, {8, 32}, {8, 33}, {5, 64}, {4, 33}, {6, 65}};
+    static const double stepUs[kMarchShapes] = {2.40, 2.40, 2.26, 1.90, 1.56, 2.14, 1.94, 1.55, 1.48, 1.80, 1.78};
     MarchPlan best; double bestCost = 1e300;
     const char *fs = getenv("VFEM_MARCH_SHAPE"), *fx = getenv("VFEM_MARCH_XC"); // experiment overrides
-    for (int s = 0; s < 7; ++s) {
+    for (int s = 0; s < kMarchShapes; ++s) {
         if (fs) s = atoi(fs);
         const int RY = shapes[s][0], ZT = shapes[s][1], NT = ((RY * ZT + 31) / 32) * 32, MINB = 512 / NT > 0 ? 512 / NT : 1;
         const int ty = marchTiles(g.E[1], RY), tz = marchTiles(g.E[2], ZT);
@@ -366,7 +370,7 @@ inline MarchPlan planMarch(const Grid<3> &g, int numSMs) {
             const int nch = marchTiles(g.E[0], XC);
             const long long ctas = (long long)ty * tz * nch;
             const long long waves = (ctas + (long long)numSMs * MINB - 1) / ((long long)numSMs * MINB);
-            const double cost = double(waves) * (std::min(XC, g.E[0]) + 2.5) * NT * MINB;
+            const double cost = double(waves) * (std::min(XC, g.E[0]) + 2.5) * stepUs[s];
             if (cost < bestCost) { bestCost = cost; best.cfg = s; best.XC = XC; best.grid = dim3(tz, ty, nch); }
             if (fx) break;
         }
@@ -391,6 +395,10 @@ inline void launchApplyMarch(const Grid<3> &g, const KhatParam &kh, bool sparse,
         VFEM_MARCH_CASE(4, 6, 64)
         VFEM_MARCH_CASE(5, 4, 64)
         VFEM_MARCH_CASE(6, 8, 32)
+        VFEM_MARCH_CASE(7, 8, 33)
+        VFEM_MARCH_CASE(8, 5, 64)
+        VFEM_MARCH_CASE(9, 4, 33)
+        VFEM_MARCH_CASE(10, 6, 65)
     }
 #undef VFEM_MARCH_CASE
 }
