@@ -59,25 +59,12 @@ static __global__ void setIdentityBlocksKernel(Real *__restrict__ W, int P, int 
 constexpr int kChainThreads = 512; // per CTA
 constexpr int kChainCluster = 8;   // portable cluster size
 
-// dot products of up to two matrix rows with the shared vector (lane-strided, fixed order) + shuffle tree
-__device__ __forceinline__ void chainRows2(const Real *__restrict__ r0, const Real *__restrict__ r1, bool two, const Real *v, int P, int lane,
-                                           Real &s0, Real &s1) {
-    Real a0 = 0.0, a1 = 0.0;
-    for (int j = lane; j < P; j += 32) {
-        const Real vj = v[j];
-        a0 = fma(r0[j], vj, a0);
-        if (two) a1 = fma(r1[j], vj, a1);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { a0 += __shfl_xor_sync(0xffffffffu, a0, o); a1 += __shfl_xor_sync(0xffffffffu, a1, o); }
-    s0 = a0; s1 = a1;
-}
-
 // One cluster walks the planes; see the header comment.  Trm[p-1]: T_p row-major, Tcm[p-1]: T_p column-major (p = 1..planes-1),
 // Sinv[p]: S_p^{-1}.  x doubles as the scratch for v; z: planes*P scratch.  Dynamic shared memory: 2*P doubles.
-// PF (P <= 2 rows per warp, <= 256 columns): the matrix rows of the NEXT chain step are fetched into registers before
-// the cluster barrier of the current one, so the L2/HBM latency of the (vector-independent) matrix overlaps the barrier.
-template <int N, bool PF>
+// Requires P <= 256 (at most 2 rows per warp, 8 columns per lane): the matrix rows of the NEXT chain step are fetched into
+// registers before the cluster barrier of the current one, so the L2/HBM latency of the (vector-independent) matrix
+// overlaps the barrier.  Larger planes use blockTriChainGridKernel below.
+template <int N>
 static __global__ void __launch_bounds__(kChainThreads) blockTriChainKernel(int P, int planes, const Real *__restrict__ Trm, const Real *__restrict__ Tcm,
                                                                             const Real *__restrict__ Sinv, const Real *__restrict__ b,
                                                                             const uint8_t *__restrict__ dmask, Real *x, Real *z) {
@@ -118,41 +105,25 @@ static __global__ void __launch_bounds__(kChainThreads) blockTriChainKernel(int 
         s0 = a0; s1 = a1;
     };
     // one chain step: out_p[i] = masked(rhs[p*P+i] - row_i(T) . cur), published to every CTA and stored to `store`
-    auto chainStep = [&](const Real *T, const Real *rhs, Real *store, int p, const Real *Tnext) {
-        if (PF) {
-            Real s0, s1;
-            dots(s0, s1);
-            if (has0) { const Real v = masked(p * P + gw, rhs[p * P + gw] - s0); publish(gw, v); if (lane == 0) store[p * P + gw] = v; }
-            if (has1) { const Real v = masked(p * P + gw + tw, rhs[p * P + gw + tw] - s1); publish(gw + tw, v); if (lane == 0) store[p * P + gw + tw] = v; }
-            if (Tnext) fetch(Tnext);
-        } else {
-            for (int i = gw; i < P; i += 2 * tw) {
-                const bool two = i + tw < P;
-                Real s0, s1;
-                chainRows2(T + size_t(i) * P, T + size_t(two ? i + tw : i) * P, two, cur, P, lane, s0, s1);
-                const Real v0 = masked(p * P + i, rhs[p * P + i] - s0);
-                publish(i, v0);
-                if (lane == 0) store[p * P + i] = v0;
-                if (two) {
-                    const Real v1 = masked(p * P + i + tw, rhs[p * P + i + tw] - s1);
-                    publish(i + tw, v1);
-                    if (lane == 0) store[p * P + i + tw] = v1;
-                }
-            }
-        }
+    auto chainStep = [&](const Real *rhs, Real *store, int p, const Real *Tnext) {
+        Real s0, s1;
+        dots(s0, s1);
+        if (has0) { const Real v = masked(p * P + gw, rhs[p * P + gw] - s0); publish(gw, v); if (lane == 0) store[p * P + gw] = v; }
+        if (has1) { const Real v = masked(p * P + gw + tw, rhs[p * P + gw + tw] - s1); publish(gw + tw, v); if (lane == 0) store[p * P + gw + tw] = v; }
+        if (Tnext) fetch(Tnext);
         cl.sync();
         Real *sw = cur; cur = nxt; nxt = sw;
     };
     // ---- forward: z_0 = b_0,  z_p = b_p - T_p z_{p-1} ----
-    if (PF && planes > 1) fetch(Trm);
+    if (planes > 1) fetch(Trm);
     for (int i = tid; i < P; i += kChainThreads) { const Real v = masked(i, b[i]); cur[i] = v; if (rank == 0) z[i] = v; }
     cl.sync();
     for (int p = 1; p < planes; ++p)
-        chainStep(Trm + size_t(p - 1) * PP, b, z, p, p + 1 < planes ? Trm + size_t(p) * PP : nullptr);
+        chainStep(b, z, p, p + 1 < planes ? Trm + size_t(p) * PP : nullptr);
     __threadfence();
     cl.sync();
     // ---- diagonal: v_p = S_p^{-1} z_p, all planes at once (v parked in x) ----
-    if (PF && planes > 1) fetch(Tcm + size_t(planes - 2) * PP);
+    if (planes > 1) fetch(Tcm + size_t(planes - 2) * PP);
     for (int row = gw; row < planes * P; row += tw) {
         const int p = row / P, i = row - p * P;
         const Real *Sr = Sinv + size_t(p) * PP + size_t(i) * P, *zp = z + size_t(p) * P;
@@ -168,7 +139,85 @@ static __global__ void __launch_bounds__(kChainThreads) blockTriChainKernel(int 
     for (int i = tid; i < P; i += kChainThreads) cur[i] = x[size_t(planes - 1) * P + i];
     __syncthreads();
     for (int p = planes - 2; p >= 0; --p)
-        chainStep(Tcm + size_t(p) * PP, x, x, p, p > 0 ? Tcm + size_t(p - 1) * PP : nullptr);
+        chainStep(x, x, p, p > 0 ? Tcm + size_t(p - 1) * PP : nullptr);
+}
+
+// Large planes (P > 256): the same three phases on the WHOLE device.  One cooperative launch; a warp owns a matrix row,
+// the plane vectors live in global memory and are staged into every CTA's shared memory at the start of a step (read
+// with ld.global.cg: other CTAs wrote them in the previous step); a grid barrier per chain step.  A lane issues all its
+// loads of a row (up to 32) before the first multiply, so a step costs about one memory round trip, and the rows of the
+// next step are prefetched into L2 before the barrier.  Dynamic shared memory: P doubles.
+constexpr int kChainGridThreads = 256;
+template <int N>
+static __global__ void __launch_bounds__(kChainGridThreads) blockTriChainGridKernel(int P, int planes, const Real *__restrict__ Trm,
+                                                                                const Real *__restrict__ Tcm, const Real *__restrict__ Sinv,
+                                                                                const Real *__restrict__ b, const uint8_t *__restrict__ dmask,
+                                                                                Real *x, Real *z) {
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ Real sv[];
+    const int lane = threadIdx.x & 31;
+    const int gw = (blockIdx.x * kChainGridThreads + threadIdx.x) >> 5, tw = (gridDim.x * kChainGridThreads) >> 5;
+    const size_t PP = size_t(P) * P;
+    auto masked = [&](int dof, Real v) { return ((dmask[dof / N] >> (dof % N)) & 1u) ? 0.0 : v; };
+    auto stage = [&](const Real *v) { // plane vector -> shared memory (block-wide)
+        __syncthreads();
+        for (int i = threadIdx.x; i < P; i += kChainGridThreads) sv[i] = __ldcg(v + i);
+        __syncthreads();
+    };
+    auto rowDot = [&](const Real *__restrict__ row) { // row . sv, all lanes return the sum
+        Real a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+        for (int base = 0; base < P; base += 1024) {
+            Real rv[32];
+#pragma unroll
+            for (int k = 0; k < 32; ++k) { const int j = base + lane + 32 * k; rv[k] = j < P ? row[j] : 0.0; }
+#pragma unroll
+            for (int k = 0; k < 32; k += 4) {
+                const int j = base + lane + 32 * k;
+                a0 = fma(rv[k], j < P ? sv[j] : 0.0, a0); a1 = fma(rv[k + 1], j + 32 < P ? sv[j + 32] : 0.0, a1);
+                a2 = fma(rv[k + 2], j + 64 < P ? sv[j + 64] : 0.0, a2); a3 = fma(rv[k + 3], j + 96 < P ? sv[j + 96] : 0.0, a3);
+            }
+        }
+        Real a = (a0 + a1) + (a2 + a3);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+        return a;
+    };
+    // the matrices do not depend on the chain: pull the rows of the NEXT step into L2 before waiting at the barrier
+    auto prefetchRows = [&](const Real *T) {
+        for (int i = gw; i < P; i += tw)
+            for (int j = lane * 16; j < P; j += 512) asm volatile("prefetch.global.L2 [%0];" ::"l"(T + size_t(i) * P + j));
+    };
+    for (int i = blockIdx.x * kChainGridThreads + threadIdx.x; i < P; i += gridDim.x * kChainGridThreads) z[i] = masked(i, b[i]);
+    if (planes > 1) prefetchRows(Trm);
+    grid.sync();
+    for (int p = 1; p < planes; ++p) { // forward
+        stage(z + size_t(p - 1) * P);
+        for (int i = gw; i < P; i += tw) {
+            const Real s = rowDot(Trm + size_t(p - 1) * PP + size_t(i) * P);
+            if (lane == 0) z[p * P + i] = masked(p * P + i, b[p * P + i] - s);
+        }
+        if (p + 1 < planes) prefetchRows(Trm + size_t(p) * PP);
+        grid.sync();
+    }
+    for (int p = 0; p < planes; ++p) { // diagonal: no dependency between the planes, only block-level staging
+        stage(z + size_t(p) * P);
+        for (int i = gw; i < P; i += tw) {
+            const Real s = rowDot(Sinv + size_t(p) * PP + size_t(i) * P);
+            if (lane == 0) x[p * P + i] = masked(p * P + i, s);
+        }
+    }
+    if (planes > 1) prefetchRows(Tcm + size_t(planes - 2) * PP);
+    grid.sync();
+    for (int p = planes - 2; p >= 0; --p) { // backward
+        stage(x + size_t(p + 1) * P);
+        for (int i = gw; i < P; i += tw) {
+            const Real s = rowDot(Tcm + size_t(p) * PP + size_t(i) * P);
+            if (lane == 0) x[p * P + i] = masked(p * P + i, __ldcg(x + p * P + i) - s);
+        }
+        if (p > 0) prefetchRows(Tcm + size_t(p - 1) * PP);
+        grid.sync();
+    }
 }
 
 } // namespace vfem

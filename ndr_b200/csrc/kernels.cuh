@@ -61,24 +61,11 @@ __host__ __device__ inline int colourCount(const Grid<N> &g, int colour) {
 // M (optional) = sum_e E_e * K0[(loc,:),(loc,:)], the node's diagonal block (MG.hh:223-225).
 // Out-of-grid neighbours read 0 and out-of-grid elements get modulus 0: branch-free, and
 // adding exact zeros leaves the result unchanged.
+// row of K(rho) u at one node from its gathered 3^N neighbourhood un[k][c] (zeros outside the grid)
 template <int N, bool WITH_M>
-__device__ __forceinline__ void fineNodeRow(const Grid<N> &g, const K0Param<N> &K, const Real *__restrict__ Ey,
-                                            const Real *__restrict__ u, const int *idx, Real *acc, Real *M) {
-    constexpr int NPE = 1 << N, KS = N * NPE, NST = ipow3(N);
-    Real un[NST][N];
-#pragma unroll
-    for (int k = 0; k < NST; ++k) {
-        int t = k, off = 0; bool ok = true;
-#pragma unroll
-        for (int d = N - 1; d >= 0; --d) {
-            int dl = t % 3 - 1; t /= 3;
-            int v = idx[d] + dl; ok = ok && (v >= 0) && (v < g.n[d]);
-            off += dl * g.ninc[d];
-        }
-        int base = flattenNode<N>(g, idx) + off;
-#pragma unroll
-        for (int c = 0; c < N; ++c) un[k][c] = ok ? u[size_t(base) * N + c] : 0.0;
-    }
+__device__ __forceinline__ void fineNodeRowCompute(const Grid<N> &g, const K0Param<N> &K, const Real *__restrict__ Ey, const int *idx,
+                                                   const Real (&un)[ipow3(N)][N], Real *acc, Real *M) {
+    constexpr int NPE = 1 << N, KS = N * NPE;
 #pragma unroll
     for (int s = 0; s < NPE; ++s) {
         int ei = 0, loc = 0; bool ok = true;
@@ -115,6 +102,27 @@ __device__ __forceinline__ void fineNodeRow(const Grid<N> &g, const K0Param<N> &
                 for (int c2 = 0; c2 < N; ++c2) M[c * N + c2] = fma(Ee, K.k[(loc * N + c) * KS + loc * N + c2], M[c * N + c2]);
         }
     }
+}
+
+template <int N, bool WITH_M>
+__device__ __forceinline__ void fineNodeRow(const Grid<N> &g, const K0Param<N> &K, const Real *__restrict__ Ey,
+                                            const Real *__restrict__ u, const int *idx, Real *acc, Real *M) {
+    constexpr int NST = ipow3(N);
+    Real un[NST][N];
+#pragma unroll
+    for (int k = 0; k < NST; ++k) {
+        int t = k, off = 0; bool ok = true;
+#pragma unroll
+        for (int d = N - 1; d >= 0; --d) {
+            int dl = t % 3 - 1; t /= 3;
+            int v = idx[d] + dl; ok = ok && (v >= 0) && (v < g.n[d]);
+            off += dl * g.ninc[d];
+        }
+        int base = flattenNode<N>(g, idx) + off;
+#pragma unroll
+        for (int c = 0; c < N; ++c) un[k][c] = ok ? u[size_t(base) * N + c] : 0.0;
+    }
+    fineNodeRowCompute<N, WITH_M>(g, K, Ey, idx, un, acc, M);
 }
 
 // ---- coarse levels: assembled 3^N-point block stencil ---------------------------------------------

@@ -285,18 +285,31 @@ void MG<N>::coarseSolve(const Real *b, Real *x) {
         comm->allreduceSum(bg.p, bg.n, stream);
         b = bg.p; x = xg.p; cmask = dmaskG.p;
     }
-    const size_t smem = size_t(2) * coarseP * sizeof(Real);
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(kChainCluster); cfg.blockDim = dim3(kChainThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = kChainCluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
     const bool pf = coarseP <= 256 && coarseP <= 2 * kChainCluster * (kChainThreads / 32);
-    auto kern = pf ? blockTriChainKernel<N, true> : blockTriChainKernel<N, false>;
-    if (smem > 48 * 1024) VFEM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    VFEM_CUDA(cudaLaunchKernelEx(&cfg, kern, coarseP, coarsePlanes, (const Real *)d_Trm.p, (const Real *)d_Tcm.p,
-                                 (const Real *)d_Sinv.p, b, cmask, x, d_z.p));
+    if (pf) { // small planes: one thread-block cluster, plane vector in distributed shared memory
+        const size_t smem = size_t(2) * coarseP * sizeof(Real);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(kChainCluster); cfg.blockDim = dim3(kChainThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = kChainCluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        VFEM_CUDA(cudaLaunchKernelEx(&cfg, blockTriChainKernel<N>, coarseP, coarsePlanes, (const Real *)d_Trm.p, (const Real *)d_Tcm.p,
+                                     (const Real *)d_Sinv.p, b, cmask, x, d_z.p));
+    } else { // large planes: the whole device, one grid barrier per chain step
+        if (chainGridBlocks == 0) {
+            int dev = 0, sms = 148;
+            VFEM_CUDA(cudaGetDevice(&dev));
+            VFEM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+            chainGridBlocks = sms;
+        }
+        int P = coarseP, planes = coarsePlanes;
+        const Real *Trm = d_Trm.p, *Tcm = d_Tcm.p, *Sinv = d_Sinv.p; Real *zp = d_z.p;
+        void *args[] = {&P, &planes, &Trm, &Tcm, &Sinv, &b, &cmask, &x, &zp};
+        const size_t smem = size_t(coarseP) * sizeof(Real);
+        if (smem > 48 * 1024) VFEM_CUDA(cudaFuncSetAttribute(blockTriChainGridKernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        VFEM_CUDA(cudaLaunchCooperativeKernel((const void *)blockTriChainGridKernel<N>, dim3(chainGridBlocks), dim3(kChainGridThreads), args, smem, stream));
+    }
     countLaunch();
     if (slab()) // the local window (ghost planes included) of the global solution
         VFEM_CUDA(cudaMemcpyAsync(xl, xg.p + size_t(coarsePlaneOffset) * Lc.g.ninc[0] * N, size_t(Lc.g.nn) * N * sizeof(Real),

@@ -53,7 +53,7 @@ struct MG : MGBase {
         bool operator==(const PrecondKey &o) const { return f == o.f && steps == o.steps && nu == o.nu && fmg == o.fmg && sym == o.sym && P == o.P && planes == o.planes; }
     };
     bool useGraphs = true, fusedSweeps = true;
-    int gsVariant = 4;              // fine-level GS: resident blocks per SM the register budget is sized for (experiment knob)
+    int gsVariant = 4;              // fine-level GS: resident CTAs per SM the register budget is sized for (2..4, experiment knob)
     cudaStream_t captureStream = nullptr;
     cudaGraphExec_t pgExec = nullptr;
     PrecondKey pgKey;
@@ -105,7 +105,7 @@ struct MG : MGBase {
     void applyKMasked(size_t l, const Real *u, Real *out);
     void smoothColoured(size_t l, Real *u, const Real *b, bool forward);               // MG.hh:336-340
     void smooth(size_t l, Real *u, const Real *b, bool forward, size_t sweeps);        // `sweeps` x smoothColoured, fused on the assembled levels
-    int sweepGridBlocks = 0;        // co-resident blocks of gsStencilSweepKernel (cooperative launch)
+    int sweepGridBlocks = 0, chainGridBlocks = 0;        // co-resident blocks of gsStencilSweepKernel (cooperative launch)
     void restriction(size_t lf, const Real *vf, Real *bc);                             // MG.hh:145-180
     void interpolate(size_t lf, const Real *xc, Real *xf, bool accumulate);            // MG.hh:115-141
     void zeroOutDirichlet(size_t l, Real *u);                                          // MG.hh:364-378

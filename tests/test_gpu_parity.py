@@ -15,6 +15,8 @@ CASES = {
     "bridge3d": (3, [4, 2, 1], [32, 16, 16], "3d/bridge.bc", 2),   # anisotropic element (1/8, 1/8, 1/16)
     "mbb2d": (2, [3, 1], [96, 32], "2d/mbb_beam.bc", 3),
 }
+# coarsest level 12x12x12: planes of 13*13*3 = 507 dofs (> 256) take the grid-wide chain kernel of coarse_solve.cuh
+BIG_COARSE = (3, [1, 1, 1], [24, 24, 24], "3d/cantilever_flexion.bc", 1)
 
 
 def rel(a, b):
@@ -127,3 +129,20 @@ def test_pcg_parity(oracle_mod, name):
     ref, ko, _ = o.mg_pcg(u0, f, 100, 1e-12, 1, 2, True)
     assert rel(got, ref) < 1e-10
     assert abs(np.sum(f * got) - np.sum(f * ref)) <= 1e-10 * abs(np.sum(f * ref))
+
+
+def test_large_coarsest_planes(oracle_mod):
+    """exact coarsest solve with planes above the cluster kernel's size (cooperative grid kernel) inside FMG / PCG"""
+    CASES["bigcoarse"] = BIG_COARSE
+    try:
+        o, g, levels = make_pair(oracle_mod, "bigcoarse")
+    finally:
+        del CASES["bigcoarse"]
+    o.mg_create(levels)
+    mg = g.multigridSolver(levels)
+    f = o.load_vector()
+    u0 = np.zeros_like(f)
+    assert rel(mg.solve(u0, f, 2, 2, fullMultigrid=True), o.mg_solve(u0, f, 2, 2, fmg=True)) < 1e-10
+    got, kg, _ = mg.preconditionedConjugateGradient(u0, f, 100, 1e-10, mgIterations=1, mgSmoothingIterations=2, fullMultigrid=True, return_info=True)
+    ref, ko, _ = o.mg_pcg(u0, f, 100, 1e-10, 1, 2, True)
+    assert kg == ko and rel(got, ref) < 1e-9
