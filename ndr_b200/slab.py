@@ -10,7 +10,7 @@ Per operator application one node plane per interior face crosses NVLink (ncclSe
 on its own stream); dot products are one-scalar all-reduces; the coarsest level is gathered and solved redundantly on
 every rank.  `torch.distributed` (NCCL on the GPUs, gloo in the CPU tests) is the control plane: it broadcasts the NCCL
 unique id and reduces the node counts of force regions.  There is no reference counterpart (the reference is TBB on
-one node); results are those of the undecomposed grid to roundoff and are asserted against the single-thread oracle.
+one node); results are those of the undecomposed grid to roundoff and are asserted against the CPU restatement in the tests.
 """
 import ctypes as C
 
