@@ -5,9 +5,11 @@
 // (a node only couples to the planes x-1, x, x+1): P = N * nodesPerPlane dofs per block.  Once per density update the
 // host runs the block LDL^T recurrence  S_0 = A_00,  T_p = A_{p,p-1} S_{p-1}^{-1},  S_p = A_pp - T_p A_{p,p-1}^T
 // (cuSOLVER potrf + cuBLAS trsm/gemm on P x P blocks) and stores S_p^{-1}, T_p explicitly, so that a solve is
-//     forward    z_p = b_p - T_p z_{p-1}            (a chain of planes-1 dependent matrix-vector products)
+//     forward    z_p = b_p - T_p z_{p-1}            (a chain of dependent matrix-vector products)
 //     diagonal   v_p = S_p^{-1} z_p                 (independent over the planes)
-//     backward   x_p = v_p - T_{p+1}^T x_{p+1}      (a chain again)
+//     backward   x_p = v_p - T_{p+1}^T x_{p+1}      (a chain again).
+// Both the factorisation and the solve run the recurrence from BOTH ends of the plane sequence towards the middle
+// plane (two independent chains, see ChainIdx), which halves the number of dependent steps.
 // done by ONE launch of ONE thread-block cluster (blockTriChainKernel): the rows of each product are spread over the
 // warps of the cluster, every CTA keeps the current plane vector in its shared memory, and a finished entry is written
 // into all CTAs' copies through distributed shared memory, so a chain step costs one cluster barrier instead of a
@@ -58,72 +60,119 @@ static __global__ void setIdentityBlocksKernel(Real *__restrict__ W, int P, int 
 
 constexpr int kChainThreads = 512; // per CTA
 constexpr int kChainCluster = 8;   // portable cluster size
+constexpr int kChainSlots = 4;     // matrix rows per warp and step: 2 chains x P rows <= kChainSlots * 128 warps
 
-// One cluster walks the planes; see the header comment.  Trm[p-1]: T_p row-major, Tcm[p-1]: T_p column-major (p = 1..planes-1),
-// Sinv[p]: S_p^{-1}.  x doubles as the scratch for v; z: planes*P scratch.  Dynamic shared memory: 2*P doubles.
-// Requires P <= 256 (at most 2 rows per warp, 8 columns per lane): the matrix rows of the NEXT chain step are fetched into
-// registers before the cluster barrier of the current one, so the L2/HBM latency of the (vector-independent) matrix
-// overlaps the barrier.  Larger planes use blockTriChainGridKernel below.
+// Index helpers of the two-ended ("burn at both ends") elimination shared by both kernels and the host factorisation.
+// Planes 0..mid-1 are eliminated downwards (chain 0), planes-1..mid+1 upwards (chain 1), plane `mid` last.
+// Block q of Trm / Tcm (row- / column-major) holds  T_{q+1} = A_{q+1,q} S_q^{-1}   for q <  mid  (chain 0)
+//                                              and  U_q     = A_{q+1,q}^T S_{q+1}^{-1} for q >= mid (chain 1).
+struct ChainIdx {
+    int planes, mid;
+    __host__ __device__ int len(int c) const { return c == 0 ? mid : planes - 1 - mid; }            // planes of chain c
+    __host__ __device__ int plane(int c, int s) const { return c == 0 ? s : planes - 1 - s; }          // s-th plane of chain c
+    __host__ __device__ int fwdBlock(int c, int s) const { return c == 0 ? s - 1 : planes - 1 - s; }   // z_s = b_s - M z_{s-1}
+    __host__ __device__ int midBlock(int c) const { return c == 0 ? mid - 1 : mid; }
+    __host__ __device__ int bwdPlane(int c, int s) const { return c == 0 ? mid - s : mid + s; }        // s = 1..len(c)
+    __host__ __device__ int bwdBlock(int c, int s) const { return c == 0 ? mid - s : mid + s - 1; }
+    __host__ __device__ int steps() const { int a = len(0), b2 = len(1); return a > b2 ? a : b2; }
+};
+
+// One cluster walks the planes; see the header comment.  x doubles as the scratch for v; z: planes*P scratch.
+// Dynamic shared memory: 4*P doubles (current / next vector of both chains).  Requires 2 P <= 512 rows per step.
+// The matrix rows of the NEXT step are fetched into registers before the cluster barrier of the current one, so the
+// L2/HBM latency of the (vector-independent) matrices overlaps the barrier.  Larger planes: blockTriChainGridKernel.
 template <int N>
-static __global__ void __launch_bounds__(kChainThreads) blockTriChainKernel(int P, int planes, const Real *__restrict__ Trm, const Real *__restrict__ Tcm,
+static __global__ void __launch_bounds__(kChainThreads) blockTriChainKernel(int P, ChainIdx ci, const Real *__restrict__ Trm, const Real *__restrict__ Tcm,
                                                                             const Real *__restrict__ Sinv, const Real *__restrict__ b,
                                                                             const uint8_t *__restrict__ dmask, Real *x, Real *z) {
     namespace cg = cooperative_groups;
     cg::cluster_group cl = cg::this_cluster();
     extern __shared__ Real sm[];
-    Real *cur = sm, *nxt = sm + P;
+    Real *cur = sm, *nxt = sm + 2 * P; // [chain][P]
     const int tid = threadIdx.x, lane = tid & 31, nw = kChainThreads / 32;
     const int ncta = int(cl.num_blocks()), rank = int(cl.block_rank());
     const int gw = rank * nw + (tid >> 5), tw = ncta * nw;
+    const int planes = ci.planes, mid = ci.mid;
     const size_t PP = size_t(P) * P;
     auto masked = [&](int dof, Real v) { return ((dmask[dof / N] >> (dof % N)) & 1u) ? 0.0 : v; };
-    // every entry is published to all CTAs' copies of the next plane vector (lanes 0..ncta-1 each serve one CTA)
-    auto publish = [&](int i, Real v) {
-        if (lane < ncta) cl.map_shared_rank(nxt, lane)[i] = v;
+    // every entry is published to all CTAs' copies of the next vectors (lanes 0..ncta-1 each serve one CTA)
+    auto publish = [&](int e, Real v) {
+        if (lane < ncta) cl.map_shared_rank(nxt, lane)[e] = v;
     };
     constexpr int JP = 8;
-    Real t0[JP], t1[JP];
-    const bool has0 = gw < P, has1 = gw + tw < P;
-    auto fetch = [&](const Real *T) { // rows gw and gw + tw of T
+    Real t[kChainSlots][JP];
+    int sc[kChainSlots], si[kChainSlots]; // chain and row of this warp's slots (-1: none)
 #pragma unroll
-        for (int j = 0; j < JP; ++j) {
-            const int c = lane + 32 * j;
-            t0[j] = (has0 && c < P) ? T[size_t(gw) * P + c] : 0.0;
-            t1[j] = (has1 && c < P) ? T[size_t(gw + tw) * P + c] : 0.0;
+    for (int k = 0; k < kChainSlots; ++k) { const int r = gw + k * tw; sc[k] = r < 2 * P ? r / P : -1; si[k] = r < 2 * P ? r - (r / P) * P : 0; }
+    // phase 0: forward step s, 1: middle, 2: backward step s  ->  matrix block of chain c, or -1 when the chain is idle
+    auto blockOf = [&](int phase, int s, int c) {
+        if (phase == 0) return s <= ci.len(c) - 1 ? ci.fwdBlock(c, s) : -1;
+        if (phase == 1) return ci.len(c) >= 1 ? ci.midBlock(c) : -1;
+        return s <= ci.len(c) ? ci.bwdBlock(c, s) : -1;
+    };
+    auto fetch = [&](int phase, int s) {
+#pragma unroll
+        for (int k = 0; k < kChainSlots; ++k) {
+            const int q = sc[k] >= 0 ? blockOf(phase, s, sc[k]) : -1;
+            const Real *row = (phase == 2 ? Tcm : Trm) + size_t(q < 0 ? 0 : q) * PP + size_t(si[k]) * P;
+#pragma unroll
+            for (int j = 0; j < JP; ++j) { const int c = lane + 32 * j; t[k][j] = (q >= 0 && c < P) ? row[c] : 0.0; }
         }
     };
-    auto dots = [&](Real &s0, Real &s1) {
-        Real a0 = 0.0, a1 = 0.0;
+    auto dots = [&](Real (&s)[kChainSlots]) {
 #pragma unroll
-        for (int j = 0; j < JP; ++j) {
-            const int c = lane + 32 * j;
-            const Real vj = c < P ? cur[c] : 0.0;
-            a0 = fma(t0[j], vj, a0); a1 = fma(t1[j], vj, a1);
+        for (int k = 0; k < kChainSlots; ++k) {
+            const Real *v = cur + (sc[k] > 0 ? P : 0);
+            Real a = 0.0;
+#pragma unroll
+            for (int j = 0; j < JP; ++j) { const int c = lane + 32 * j; a = fma(t[k][j], c < P ? v[c] : 0.0, a); }
+            s[k] = a;
         }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) { a0 += __shfl_xor_sync(0xffffffffu, a0, o); a1 += __shfl_xor_sync(0xffffffffu, a1, o); }
-        s0 = a0; s1 = a1;
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+            for (int k = 0; k < kChainSlots; ++k) s[k] += __shfl_xor_sync(0xffffffffu, s[k], o);
     };
-    // one chain step: out_p[i] = masked(rhs[p*P+i] - row_i(T) . cur), published to every CTA and stored to `store`
-    auto chainStep = [&](const Real *rhs, Real *store, int p, const Real *Tnext) {
-        Real s0, s1;
-        dots(s0, s1);
-        if (has0) { const Real v = masked(p * P + gw, rhs[p * P + gw] - s0); publish(gw, v); if (lane == 0) store[p * P + gw] = v; }
-        if (has1) { const Real v = masked(p * P + gw + tw, rhs[p * P + gw + tw] - s1); publish(gw + tw, v); if (lane == 0) store[p * P + gw + tw] = v; }
-        if (Tnext) fetch(Tnext);
+    // one step of both chains; the registers already hold its matrix rows, (nphase, ns) names the step to prefetch
+    auto chainStep = [&](int phase, int s, int nphase, int ns) {
+        Real d[kChainSlots];
+        dots(d);
+#pragma unroll
+        for (int k = 0; k < kChainSlots; ++k) {
+            if (sc[k] < 0) continue;
+            const int c = sc[k], i = si[k], e = c * P + i;
+            if (blockOf(phase, s, c) < 0) { publish(e, phase == 1 ? 0.0 : cur[e]); continue; } // idle chain: keep its vector
+            if (phase == 1) { publish(e, d[k]); continue; }                                     // partial sums of the middle plane
+            const int pl = phase == 0 ? ci.plane(c, s) : ci.bwdPlane(c, s);
+            const Real rhs = phase == 0 ? b[pl * P + i] : x[pl * P + i];
+            const Real v = masked(pl * P + i, rhs - d[k]);
+            publish(e, v);
+            if (lane == 0) (phase == 0 ? z : x)[pl * P + i] = v;
+        }
+        if (nphase >= 0) fetch(nphase, ns);
         cl.sync();
         Real *sw = cur; cur = nxt; nxt = sw;
     };
-    // ---- forward: z_0 = b_0,  z_p = b_p - T_p z_{p-1} ----
-    if (planes > 1) fetch(Trm);
-    for (int i = tid; i < P; i += kChainThreads) { const Real v = masked(i, b[i]); cur[i] = v; if (rank == 0) z[i] = v; }
+    // ---- forward: both chains start from their end planes ----
+    const int S = ci.steps();
+    fetch(S > 1 ? 0 : 1, 1);
+    for (int i = tid; i < P; i += kChainThreads) {
+        const Real v0 = masked(i, b[i]), v1 = masked((planes - 1) * P + i, b[(planes - 1) * P + i]);
+        cur[i] = v0; cur[P + i] = v1;
+        if (rank == 0) { if (ci.len(0) >= 1) z[i] = v0; if (ci.len(1) >= 1) z[(planes - 1) * P + i] = v1; }
+    }
     cl.sync();
-    for (int p = 1; p < planes; ++p)
-        chainStep(b, z, p, p + 1 < planes ? Trm + size_t(p) * PP : nullptr);
+    for (int s = 1; s <= S - 1; ++s) chainStep(0, s, s + 1 <= S - 1 ? 0 : 1, s + 1);
+    // ---- middle plane: z_mid = b_mid - T_mid z_{mid-1} - U_mid w_{mid+1} ----
+    chainStep(1, 0, -1, 0);
+    for (int i = tid; i < P; i += kChainThreads) {
+        const Real v = masked(mid * P + i, b[mid * P + i] - cur[i] - cur[P + i]);
+        if (rank == 0) z[mid * P + i] = v;
+    }
     __threadfence();
     cl.sync();
     // ---- diagonal: v_p = S_p^{-1} z_p, all planes at once (v parked in x) ----
-    if (planes > 1) fetch(Tcm + size_t(planes - 2) * PP);
+    if (S >= 1) fetch(2, 1);
     for (int row = gw; row < planes * P; row += tw) {
         const int p = row / P, i = row - p * P;
         const Real *Sr = Sinv + size_t(p) * PP + size_t(i) * P, *zp = z + size_t(p) * P;
@@ -135,11 +184,10 @@ static __global__ void __launch_bounds__(kChainThreads) blockTriChainKernel(int 
     }
     __threadfence();
     cl.sync();
-    // ---- backward: x_last = v_last,  x_p = v_p - T_{p+1}^T x_{p+1}  (column i of T_{p+1} is contiguous in Tcm) ----
-    for (int i = tid; i < P; i += kChainThreads) cur[i] = x[size_t(planes - 1) * P + i];
+    // ---- backward: outwards from x_mid = v_mid ----
+    for (int i = tid; i < P; i += kChainThreads) { const Real v = x[size_t(mid) * P + i]; cur[i] = v; cur[P + i] = v; }
     __syncthreads();
-    for (int p = planes - 2; p >= 0; --p)
-        chainStep(x, x, p, p > 0 ? Tcm + size_t(p - 1) * PP : nullptr);
+    for (int s = 1; s <= S; ++s) chainStep(2, s, s + 1 <= S ? 2 : -1, s + 1);
 }
 
 // Large planes (P > 256): the same three phases on the WHOLE device.  One cooperative launch; a warp owns a matrix row,
@@ -149,23 +197,24 @@ static __global__ void __launch_bounds__(kChainThreads) blockTriChainKernel(int 
 // next step are prefetched into L2 before the barrier.  Dynamic shared memory: P doubles.
 constexpr int kChainGridThreads = 256;
 template <int N>
-static __global__ void __launch_bounds__(kChainGridThreads) blockTriChainGridKernel(int P, int planes, const Real *__restrict__ Trm,
+static __global__ void __launch_bounds__(kChainGridThreads) blockTriChainGridKernel(int P, ChainIdx ci, const Real *__restrict__ Trm,
                                                                                 const Real *__restrict__ Tcm, const Real *__restrict__ Sinv,
                                                                                 const Real *__restrict__ b, const uint8_t *__restrict__ dmask,
                                                                                 Real *x, Real *z) {
     namespace cg = cooperative_groups;
     cg::grid_group grid = cg::this_grid();
-    extern __shared__ Real sv[];
-    const int lane = threadIdx.x & 31;
-    const int gw = (blockIdx.x * kChainGridThreads + threadIdx.x) >> 5, tw = (gridDim.x * kChainGridThreads) >> 5;
+    extern __shared__ Real sv[]; // [chain][P]
+    const int lane = threadIdx.x & 31, gtid = blockIdx.x * kChainGridThreads + threadIdx.x, gthreads = gridDim.x * kChainGridThreads;
+    const int gw = gtid >> 5, tw = gthreads >> 5;
+    const int planes = ci.planes, mid = ci.mid, S = ci.steps();
     const size_t PP = size_t(P) * P;
     auto masked = [&](int dof, Real v) { return ((dmask[dof / N] >> (dof % N)) & 1u) ? 0.0 : v; };
-    auto stage = [&](const Real *v) { // plane vector -> shared memory (block-wide)
+    auto stage = [&](const Real *v0, const Real *v1) { // plane vectors of both chains -> shared memory (block-wide)
         __syncthreads();
-        for (int i = threadIdx.x; i < P; i += kChainGridThreads) sv[i] = __ldcg(v + i);
+        for (int i = threadIdx.x; i < P; i += kChainGridThreads) { sv[i] = v0 ? __ldcg(v0 + i) : 0.0; sv[P + i] = v1 ? __ldcg(v1 + i) : 0.0; }
         __syncthreads();
     };
-    auto rowDot = [&](const Real *__restrict__ row) { // row . sv, all lanes return the sum
+    auto rowDot = [&](const Real *__restrict__ row, const Real *v) { // row . v (v in shared memory), all lanes return the sum
         Real a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
         for (int base = 0; base < P; base += 1024) {
             Real rv[32];
@@ -174,8 +223,8 @@ static __global__ void __launch_bounds__(kChainGridThreads) blockTriChainGridKer
 #pragma unroll
             for (int k = 0; k < 32; k += 4) {
                 const int j = base + lane + 32 * k;
-                a0 = fma(rv[k], j < P ? sv[j] : 0.0, a0); a1 = fma(rv[k + 1], j + 32 < P ? sv[j + 32] : 0.0, a1);
-                a2 = fma(rv[k + 2], j + 64 < P ? sv[j + 64] : 0.0, a2); a3 = fma(rv[k + 3], j + 96 < P ? sv[j + 96] : 0.0, a3);
+                a0 = fma(rv[k], j < P ? v[j] : 0.0, a0); a1 = fma(rv[k + 1], j + 32 < P ? v[j + 32] : 0.0, a1);
+                a2 = fma(rv[k + 2], j + 64 < P ? v[j + 64] : 0.0, a2); a3 = fma(rv[k + 3], j + 96 < P ? v[j + 96] : 0.0, a3);
             }
         }
         Real a = (a0 + a1) + (a2 + a3);
@@ -183,39 +232,71 @@ static __global__ void __launch_bounds__(kChainGridThreads) blockTriChainGridKer
         for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
         return a;
     };
-    // the matrices do not depend on the chain: pull the rows of the NEXT step into L2 before waiting at the barrier
-    auto prefetchRows = [&](const Real *T) {
-        for (int i = gw; i < P; i += tw)
-            for (int j = lane * 16; j < P; j += 512) asm volatile("prefetch.global.L2 [%0];" ::"l"(T + size_t(i) * P + j));
-    };
-    for (int i = blockIdx.x * kChainGridThreads + threadIdx.x; i < P; i += gridDim.x * kChainGridThreads) z[i] = masked(i, b[i]);
-    if (planes > 1) prefetchRows(Trm);
-    grid.sync();
-    for (int p = 1; p < planes; ++p) { // forward
-        stage(z + size_t(p - 1) * P);
-        for (int i = gw; i < P; i += tw) {
-            const Real s = rowDot(Trm + size_t(p - 1) * PP + size_t(i) * P);
-            if (lane == 0) z[p * P + i] = masked(p * P + i, b[p * P + i] - s);
+    // the matrices do not depend on the chains: pull the rows of the NEXT step into L2 before waiting at the barrier
+    auto prefetchStep = [&](const Real *T, int q0, int q1) {
+        for (int r = gw; r < 2 * P; r += tw) {
+            const int c = r / P, i = r - c * P, q = c == 0 ? q0 : q1;
+            if (q < 0) continue;
+            for (int j = lane * 16; j < P; j += 512) asm volatile("prefetch.global.L2 [%0];" ::"l"(T + size_t(q) * PP + size_t(i) * P + j));
         }
-        if (p + 1 < planes) prefetchRows(Trm + size_t(p) * PP);
+    };
+    auto fwdBlock = [&](int c, int s) { return s <= ci.len(c) - 1 ? ci.fwdBlock(c, s) : -1; };
+    auto midBlock = [&](int c) { return ci.len(c) >= 1 ? ci.midBlock(c) : -1; };
+    auto bwdBlock = [&](int c, int s) { return s <= ci.len(c) ? ci.bwdBlock(c, s) : -1; };
+    // ---- forward ----
+    for (int i = gtid; i < P; i += gthreads) {
+        if (ci.len(0) >= 1) z[i] = masked(i, b[i]);
+        if (ci.len(1) >= 1) z[(planes - 1) * P + i] = masked((planes - 1) * P + i, b[(planes - 1) * P + i]);
+    }
+    if (S > 1) prefetchStep(Trm, fwdBlock(0, 1), fwdBlock(1, 1)); else prefetchStep(Trm, midBlock(0), midBlock(1));
+    grid.sync();
+    for (int s = 1; s <= S - 1; ++s) {
+        const int q0 = fwdBlock(0, s), q1 = fwdBlock(1, s);
+        stage(q0 >= 0 ? z + size_t(ci.plane(0, s - 1)) * P : nullptr, q1 >= 0 ? z + size_t(ci.plane(1, s - 1)) * P : nullptr);
+        for (int r = gw; r < 2 * P; r += tw) {
+            const int c = r / P, i = r - c * P, q = c == 0 ? q0 : q1;
+            if (q < 0) continue;
+            const int pl = ci.plane(c, s);
+            const Real d = rowDot(Trm + size_t(q) * PP + size_t(i) * P, sv + c * P);
+            if (lane == 0) z[pl * P + i] = masked(pl * P + i, b[pl * P + i] - d);
+        }
+        if (s + 1 <= S - 1) prefetchStep(Trm, fwdBlock(0, s + 1), fwdBlock(1, s + 1)); else prefetchStep(Trm, midBlock(0), midBlock(1));
         grid.sync();
     }
-    for (int p = 0; p < planes; ++p) { // diagonal: no dependency between the planes, only block-level staging
-        stage(z + size_t(p) * P);
+    { // ---- middle plane: partial products parked in x[0 .. 2P) (x is not in use yet) ----
+        const int q0 = midBlock(0), q1 = midBlock(1);
+        stage(q0 >= 0 ? z + size_t(mid - 1) * P : nullptr, q1 >= 0 ? z + size_t(mid + 1) * P : nullptr);
+        for (int r = gw; r < 2 * P; r += tw) {
+            const int c = r / P, i = r - c * P, q = c == 0 ? q0 : q1;
+            if (q < 0) continue;
+            const Real d = rowDot(Trm + size_t(q) * PP + size_t(i) * P, sv + c * P);
+            if (lane == 0) x[c * P + i] = d;
+        }
+        grid.sync();
+        for (int i = gtid; i < P; i += gthreads)
+            z[mid * P + i] = masked(mid * P + i, b[mid * P + i] - (q0 >= 0 ? __ldcg(x + i) : 0.0) - (q1 >= 0 ? __ldcg(x + P + i) : 0.0));
+        grid.sync();
+    }
+    for (int p = 0; p < planes; ++p) { // ---- diagonal: no dependency between the planes, only block-level staging ----
+        stage(z + size_t(p) * P, nullptr);
         for (int i = gw; i < P; i += tw) {
-            const Real s = rowDot(Sinv + size_t(p) * PP + size_t(i) * P);
-            if (lane == 0) x[p * P + i] = masked(p * P + i, s);
+            const Real d = rowDot(Sinv + size_t(p) * PP + size_t(i) * P, sv);
+            if (lane == 0) x[p * P + i] = masked(p * P + i, d);
         }
     }
-    if (planes > 1) prefetchRows(Tcm + size_t(planes - 2) * PP);
+    if (S >= 1) prefetchStep(Tcm, bwdBlock(0, 1), bwdBlock(1, 1));
     grid.sync();
-    for (int p = planes - 2; p >= 0; --p) { // backward
-        stage(x + size_t(p + 1) * P);
-        for (int i = gw; i < P; i += tw) {
-            const Real s = rowDot(Tcm + size_t(p) * PP + size_t(i) * P);
-            if (lane == 0) x[p * P + i] = masked(p * P + i, __ldcg(x + p * P + i) - s);
+    for (int s = 1; s <= S; ++s) { // ---- backward, outwards from the middle plane ----
+        const int q0 = bwdBlock(0, s), q1 = bwdBlock(1, s);
+        stage(q0 >= 0 ? x + size_t(ci.bwdPlane(0, s - 1)) * P : nullptr, q1 >= 0 ? x + size_t(ci.bwdPlane(1, s - 1)) * P : nullptr);
+        for (int r = gw; r < 2 * P; r += tw) {
+            const int c = r / P, i = r - c * P, q = c == 0 ? q0 : q1;
+            if (q < 0) continue;
+            const int pl = ci.bwdPlane(c, s);
+            const Real d = rowDot(Tcm + size_t(q) * PP + size_t(i) * P, sv + c * P);
+            if (lane == 0) x[pl * P + i] = masked(pl * P + i, __ldcg(x + pl * P + i) - d);
         }
-        if (p > 0) prefetchRows(Tcm + size_t(p - 1) * PP);
+        if (s + 1 <= S) prefetchStep(Tcm, bwdBlock(0, s + 1), bwdBlock(1, s + 1));
         grid.sync();
     }
 }

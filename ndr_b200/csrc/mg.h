@@ -38,7 +38,10 @@ struct MG : MGBase {
     // coarsest level: block-tridiagonal Cholesky over the node planes of axis 0 (coarse_solve.cuh)
     DevBuf<Real> d_blkD, d_blkW, d_blkLo;   // S_p -> its Cholesky factor C_p, W_p = C_p^{-1}, A_{p+1,p}
     DevBuf<Real> d_Sinv, d_Trm, d_Tcm, d_z; // S_p^{-1}, T_p (row- and column-major), chain scratch
-    int coarseP = 0, coarsePlanes = 0;
+    int coarseP = 0, coarsePlanes = 0, coarseMid = 0;
+    void *cusolverHandle2 = nullptr, *cublasHandle2 = nullptr; // second lane of the two-ended factorisation
+    cudaStream_t factorStream = nullptr;
+    cudaEvent_t factorFork = nullptr, factorJoin = nullptr;
     int coarseDofs = 0;
     void *cublasHandle = nullptr;
     unsigned long long builtVersion = 0;
