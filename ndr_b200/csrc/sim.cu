@@ -196,35 +196,89 @@ const Real *Sim<N>::moduli() {
     return d_Ey.p;
 }
 
+// K u restricted to the element layers [layerLo, layerHi) of the local grid, by viewing the grid from layer layerLo on
+// (the kernels do not depend on the absolute plane index).  Node planes layerLo+1 .. layerHi-1 (and the grid's own
+// boundary planes) receive complete rows, the two edge planes of the view partial ones.
 template <int N>
 template <int MODE>
-void Sim<N>::applyFine(const Real *u, const Real *b, const uint8_t *mask, Real *out) {
+void Sim<N>::applyFineRange(const Real *u, const Real *b, const uint8_t *mask, Real *out, int layerLo_, int layerHi_, cudaStream_t st) {
     const Real *Ey = moduli();
-    // slab solver: the element layers below computeLo only feed ghost planes nobody reads - skip them by viewing the
-    // grid from layer computeLo on (the kernels do not depend on the absolute plane index)
     Grid<N> gv = g;
-    if (computeLo > 0) {
+    const MarchPlan *plan = &marchPlan;
+    if (layerLo_ > 0 || layerHi_ < g.E[0]) {
         int E[N];
         for (int d = 0; d < N; ++d) E[d] = g.E[d];
-        E[0] -= computeLo;
+        E[0] = layerHi_ - layerLo_;
         gv = makeGrid<N>(E);
-        const size_t po = size_t(computeLo) * g.ninc[0];
-        u += po * N; out += po * N; Ey += size_t(computeLo) * g.einc[0];
+        const size_t po = size_t(layerLo_) * g.ninc[0];
+        u += po * N; out += po * N; Ey += size_t(layerLo_) * g.einc[0];
         if (b) b += po * N;
         if (mask) mask += po;
-        if (N == 3 && computeLoPlanned != computeLo) {
-            int dev = 0, sms = 148;
-            if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-            marchPlanView = planMarch(reinterpret_cast<const Grid<3> &>(gv), sms > 0 ? sms : 148);
-            computeLoPlanned = computeLo;
+        if (N == 3) {
+            auto it = viewPlans.find(E[0]);
+            if (it == viewPlans.end()) {
+                int dev = 0, sms = 148;
+                if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+                it = viewPlans.emplace(E[0], planMarch(reinterpret_cast<const Grid<3> &>(gv), sms > 0 ? sms : 148)).first;
+            }
+            plan = &it->second;
         }
     }
     if (useMarch())
-        launchApplyMarch<MODE>(reinterpret_cast<const Grid<3> &>(gv), Khat, khatStructure == 2 && applyVariant != 2, computeLo > 0 ? marchPlanView : marchPlan,
-                               Ey, u, b, mask, out, stream);
+        launchApplyMarch<MODE>(reinterpret_cast<const Grid<3> &>(gv), Khat, khatStructure == 2 && applyVariant != 2, *plan, Ey, u, b, mask, out, st);
     else
-        applyFineKernel<N, MODE><<<(gv.nn + kBlock - 1) / kBlock, kBlock, 0, stream>>>(gv, K0, Ey, u, b, mask, out);
+        applyFineKernel<N, MODE><<<(gv.nn + kBlock - 1) / kBlock, kBlock, 0, st>>>(gv, K0, Ey, u, b, mask, out);
     VFEM_CHECK_LAUNCH(); countLaunch();
+}
+
+// slab solver: the element layers below computeLo only feed ghost planes nobody reads - skipped
+template <int N>
+template <int MODE>
+void Sim<N>::applyFine(const Real *u, const Real *b, const uint8_t *mask, Real *out) {
+    applyFineRange<MODE>(u, b, mask, out, computeLo, g.E[0], stream);
+}
+
+// Reference-facing call with HOST arrays (applyK(numpy) -> numpy): instead of copy-in / kernel / copy-out, the grid is cut
+// into chunks of node planes along axis 0 and the three stages are pipelined over two copy streams and the compute stream,
+// so host->device and device->host traffic overlap (PCIe is full duplex) and the kernel time disappears behind them.
+// Chunk k owns the node planes [a_k, b_k); its kernel covers the element layers [a_k - 1, b_k) and therefore also writes
+// PARTIAL rows into plane a_k - 1 (owned by chunk k-1: its copy-out must have finished) and plane b_k (rewritten,
+// complete, by chunk k+1).
+template <int N>
+void Sim<N>::applyKHost(const Real *hu, Real *hout) {
+    const size_t nd = numDofs(), pd = size_t(g.ninc[0]) * N;
+    if (hostIn.n != nd) { hostIn.alloc(nd); hostOut.alloc(nd); }
+    if (!h2dStream) {
+        VFEM_CUDA(cudaStreamCreateWithFlags(&h2dStream, cudaStreamNonBlocking));
+        VFEM_CUDA(cudaStreamCreateWithFlags(&d2hStream, cudaStreamNonBlocking));
+        VFEM_CUDA(cudaStreamCreateWithFlags(&hostComputeStream, cudaStreamNonBlocking));
+        for (int k = 0; k < kHostChunks; ++k) {
+            VFEM_CUDA(cudaEventCreateWithFlags(&evIn[k], cudaEventDisableTiming));
+            VFEM_CUDA(cudaEventCreateWithFlags(&evKernel[k], cudaEventDisableTiming));
+            VFEM_CUDA(cudaEventCreateWithFlags(&evOut[k], cudaEventDisableTiming));
+        }
+    }
+    moduli(); // refresh E(rho) on the main stream if stale, then make the side streams see it
+    VFEM_CUDA(cudaStreamSynchronize(stream));
+    const int E0 = g.E[0], planes = g.n[0];
+    const int C = std::max(1, std::min(kHostChunks, E0 / 4));
+    auto bound = [&](int k) { return k >= C ? planes : int((long long)E0 * k / C); }; // chunk k owns node planes [bound(k), bound(k+1))
+    for (int k = 0; k < C; ++k) { // inputs: chunk k's kernel needs the node planes up to bound(k+1) inclusive
+        const int p0 = k == 0 ? 0 : std::min(bound(k) + 1, planes), p1 = std::min(bound(k + 1) + 1, planes);
+        if (p1 > p0) VFEM_CUDA(cudaMemcpyAsync(hostIn.p + size_t(p0) * pd, hu + size_t(p0) * pd, size_t(p1 - p0) * pd * sizeof(Real), cudaMemcpyHostToDevice, h2dStream));
+        VFEM_CUDA(cudaEventRecord(evIn[k], h2dStream));
+    }
+    for (int k = 0; k < C; ++k) {
+        const int a = bound(k), bnd = bound(k + 1);
+        VFEM_CUDA(cudaStreamWaitEvent(hostComputeStream, evIn[k], 0));
+        if (k > 0) VFEM_CUDA(cudaStreamWaitEvent(hostComputeStream, evOut[k - 1], 0));
+        applyFineRange<0>(hostIn.p, nullptr, nullptr, hostOut.p, std::max(a - 1, 0), std::min(bnd, E0), hostComputeStream);
+        VFEM_CUDA(cudaEventRecord(evKernel[k], hostComputeStream));
+        VFEM_CUDA(cudaStreamWaitEvent(d2hStream, evKernel[k], 0));
+        VFEM_CUDA(cudaMemcpyAsync(hout + size_t(a) * pd, hostOut.p + size_t(a) * pd, size_t(bnd - a) * pd * sizeof(Real), cudaMemcpyDeviceToHost, d2hStream));
+        VFEM_CUDA(cudaEventRecord(evOut[k], d2hStream));
+    }
+    VFEM_CUDA(cudaStreamSynchronize(d2hStream));
 }
 
 template <int N>

@@ -6,6 +6,7 @@
 #include "common.h"
 #include "apply_march.cuh"
 #include <cmath>
+#include <map>
 #include <memory>
 
 namespace vfem {
@@ -50,11 +51,20 @@ struct Sim : SimBase {
     // with globalE0 layers along axis 0.  mn/mx/spacing/h describe the GLOBAL domain, so node positions (and with them
     // the boundary-condition regions) and K0 are bit-identical to the undecomposed grid's.
     int layerLo = 0, globalE0 = 0;
-    int computeLo = 0, computeLoPlanned = -1; // first local element layer K u is evaluated on (set by the slab solver)
-    MarchPlan marchPlanView;
+    int computeLo = 0;                        // first local element layer K u is evaluated on (set by the slab solver)
+    std::map<int, MarchPlan> viewPlans;       // march plans of sub-grid views, keyed by their layer count
+    // pipelined host-array apply (applyKHost)
+    static constexpr int kHostChunks = 4;
+    DevBuf<Real> hostIn, hostOut;
+    cudaStream_t h2dStream = nullptr, d2hStream = nullptr, hostComputeStream = nullptr;
+    cudaEvent_t evIn[kHostChunks] = {}, evKernel[kHostChunks] = {}, evOut[kHostChunks] = {};
 
     // elems: local element counts; globalE0 = 0 means "not a slab" (the local grid is the whole grid)
     Sim(const Real *bbmin, const Real *bbmax, const size_t *elems, size_t globalE0 = 0, size_t layerLo = 0);
+    ~Sim() override {
+        for (cudaStream_t st : {h2dStream, d2hStream, hostComputeStream}) if (st) cudaStreamDestroy(st);
+        for (int k = 0; k < kHostChunks; ++k) for (cudaEvent_t e : {evIn[k], evKernel[k], evOut[k]}) if (e) cudaEventDestroy(e);
+    }
 
     // TPS.hh:274-279
     void nodePosition(size_t ni, Real *p) const {
@@ -93,6 +103,8 @@ struct Sim : SimBase {
     void applyK(const Real *u, Real *out);    // TPS.hh:905-952
     // MODE 0: K u; 1: mask(b - K u); 2: mask(K u)   (fine level; MG.hh:401-413, 719-720)
     template <int MODE> void applyFine(const Real *u, const Real *b, const uint8_t *mask, Real *out);
+    template <int MODE> void applyFineRange(const Real *u, const Real *b, const uint8_t *mask, Real *out, int layerLo, int layerHi, cudaStream_t st);
+    void applyKHost(const Real *hu, Real *hout);  // host arrays in / out, copies pipelined with the kernel
     void complianceGradient(const Real *u, Real *g); // TPS.hh:730-751
 };
 
