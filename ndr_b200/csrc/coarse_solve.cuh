@@ -172,16 +172,38 @@ static __global__ void __launch_bounds__(kChainThreads) blockTriChainKernel(int 
     __threadfence();
     cl.sync();
     // ---- diagonal: v_p = S_p^{-1} z_p, all planes at once (v parked in x) ----
-    if (S >= 1) fetch(2, 1);
-    for (int row = gw; row < planes * P; row += tw) {
-        const int p = row / P, i = row - p * P;
-        const Real *Sr = Sinv + size_t(p) * PP + size_t(i) * P, *zp = z + size_t(p) * P;
-        Real a = 0.0;
-        for (int j = lane; j < P; j += 32) a = fma(Sr[j], zp[j], a);
+    // (4 rows per warp at a time, all their loads issued before the first multiply: the phase is L2-latency bound)
+    for (int row0 = gw; row0 < planes * P; row0 += kChainSlots * tw) {
+        Real sv4[kChainSlots][JP];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
-        if (lane == 0) x[row] = masked(row, a);
+        for (int k = 0; k < kChainSlots; ++k) {
+            const int row = row0 + k * tw;
+            const bool ok = row < planes * P;
+            const Real *Sr = Sinv + size_t(ok ? row : 0) * P; // row (p, i) of the stacked S^{-1} blocks: (p*P + i)*P
+#pragma unroll
+            for (int j = 0; j < JP; ++j) { const int c = lane + 32 * j; sv4[k][j] = (ok && c < P) ? Sr[c] : 0.0; }
+        }
+        Real acc[kChainSlots];
+#pragma unroll
+        for (int k = 0; k < kChainSlots; ++k) {
+            const int row = row0 + k * tw, p = row < planes * P ? row / P : 0;
+            const Real *zp = z + size_t(p) * P;
+            Real a = 0.0;
+#pragma unroll
+            for (int j = 0; j < JP; ++j) { const int c = lane + 32 * j; a = fma(sv4[k][j], c < P ? zp[c] : 0.0, a); }
+            acc[k] = a;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+            for (int k = 0; k < kChainSlots; ++k) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
+#pragma unroll
+        for (int k = 0; k < kChainSlots; ++k) {
+            const int row = row0 + k * tw;
+            if (lane == 0 && row < planes * P) x[row] = masked(row, acc[k]);
+        }
     }
+    if (S >= 1) fetch(2, 1);
     __threadfence();
     cl.sync();
     // ---- backward: outwards from x_mid = v_mid ----

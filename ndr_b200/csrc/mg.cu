@@ -413,6 +413,7 @@ void MG<N>::smooth(size_t l, Real *u, const Real *b, bool forward, size_t sweeps
         VFEM_CUDA(cudaGetDevice(&dev));
         VFEM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
         VFEM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, gsStencilSweepKernel<N>, kWarpBlock, 0));
+        if (const char *v = getenv("VFEM_SWEEP_BPS")) per = std::min(per, std::max(1, atoi(v)));
         sweepGridBlocks = sms * (per > 0 ? per : 1);
     }
     long long most = 1;
