@@ -119,6 +119,7 @@ void vfem_comm_destroy(vfem_comm_t h);
 int vfem_mg_create_slab(vfem_tps_t tps_local, size_t num_coarsening_levels, vfem_comm_t comm, vfem_mg_t *out); /* collective */
 int vfem_mg_owned_planes(vfem_mg_t h, size_t l, size_t *first, size_t *last);       /* owned node planes (inclusive) of level l, local indices */
 int vfem_mg_exchange(vfem_mg_t h, size_t l, double *v_device, int memspace);        /* refresh the ghost planes of a level-l vector (collective) */
+int vfem_mg_apply_k_halo(vfem_mg_t h, double *u_device, double *out_device, int memspace); /* ghost planes of u refreshed + out = K u on the local grid (owned planes valid); the shift overlaps the interior layers (collective) */
 int vfem_mg_dot(vfem_mg_t h, const double *a, const double *b, int memspace, double *result); /* dot product over the owned dofs of all ranks (collective) */
 
 /* ---- MultigridComplianceObjective --------------------------------------------------------------- */

@@ -139,7 +139,7 @@ __device__ __forceinline__ void marchLayer(const KhatParam &kh, const Real (&Fol
 template <int MODE, bool SPARSE, int RY, int ZT>
 __global__ void __launch_bounds__(MarchCfg<RY, ZT>::NT, MarchCfg<RY, ZT>::MINB)
 applyMarchKernel(Grid<3> g, KhatParam kh, const Real *__restrict__ Ey, const Real *__restrict__ u, const Real *__restrict__ b,
-                 const uint8_t *__restrict__ dmask, Real *__restrict__ out, int XC) {
+                 const uint8_t *__restrict__ dmask, Real *__restrict__ out, int XC, int edgeSkip) {
     constexpr int XS = MarchCfg<RY, ZT>::XS;
     __shared__ Real sYx[2][RY][3][ZT];   // row ry -> slot ry+1 : y-stage part for node row y+1
     __shared__ Real sX[2][RY][XS][6];    // zh of a thread whose z+1 neighbour sits in the next warp
@@ -168,7 +168,7 @@ applyMarchKernel(Grid<3> g, KhatParam kh, const Real *__restrict__ Ey, const Rea
                 ((live && y < ny && z < nz && ownY && ownZ) ? MF_STORE : 0u) | ((live && ry + 1 < RY) ? MF_YSEND : 0u) |
                 ((live && ry > 0) ? MF_YRECV : 0u) | (prevInWarp ? MF_PREV : 0u) | ((spz && y < ny && ownY) ? MF_SPSTORE : 0u) |
                 (top ? MF_TOP : 0u) | ((top && z < nz && ownZ) ? MF_TOPSTORE : 0u) | ((z + 1 < nz) ? MF_DZ : 0u) |
-                (blockIdx.z == 0 ? MF_CHUNK0 : 0u);
+                ((blockIdx.z == 0 && !(edgeSkip & 1)) ? MF_CHUNK0 : 0u);
         // addresses are clamped into the grid instead of predicating the loads: an out-of-grid node only ever
         // feeds element columns whose modulus is forced to 0 (MF_COL clear), so its (finite) value is irrelevant
         const int yc = min(y, ny - 1), yb = min(y + 1, ny - 1), zc = min(z, nz - 1);
@@ -298,7 +298,7 @@ applyMarchKernel(Grid<3> g, KhatParam kh, const Real *__restrict__ Ey, const Rea
         }
     };
 
-    const int nIter = (x1 - x0) + (x1 == Ex ? 1 : 0);
+    const int nIter = (x1 - x0) + ((x1 == Ex && !(edgeSkip & 2)) ? 1 : 0); // edgeSkip: the grid is a view whose first / last plane is partial
     for (int it = 0; it < nIter; it += 2) { // two steps per trip so the face registers ping-pong without copies
         step(it, FA, FB);
         if (it + 1 >= nIter) break;
@@ -381,11 +381,11 @@ inline MarchPlan planMarch(const Grid<3> &g, int numSMs) {
 
 template <int MODE>
 inline void launchApplyMarch(const Grid<3> &g, const KhatParam &kh, bool sparse, const MarchPlan &pl, const Real *Ey, const Real *u,
-                             const Real *b, const uint8_t *dmask, Real *out, cudaStream_t stream) {
+                             const Real *b, const uint8_t *dmask, Real *out, cudaStream_t stream, int edgeSkip = 0) {
 #define VFEM_MARCH_CASE(S, RY, ZT)                                                                                             \
     case S:                                                                                                                    \
-        if (sparse) applyMarchKernel<MODE, true, RY, ZT><<<pl.grid, MarchCfg<RY, ZT>::NT, 0, stream>>>(g, kh, Ey, u, b, dmask, out, pl.XC); \
-        else applyMarchKernel<MODE, false, RY, ZT><<<pl.grid, MarchCfg<RY, ZT>::NT, 0, stream>>>(g, kh, Ey, u, b, dmask, out, pl.XC);      \
+        if (sparse) applyMarchKernel<MODE, true, RY, ZT><<<pl.grid, MarchCfg<RY, ZT>::NT, 0, stream>>>(g, kh, Ey, u, b, dmask, out, pl.XC, edgeSkip); \
+        else applyMarchKernel<MODE, false, RY, ZT><<<pl.grid, MarchCfg<RY, ZT>::NT, 0, stream>>>(g, kh, Ey, u, b, dmask, out, pl.XC, edgeSkip);      \
         break;
     switch (pl.cfg) {
         VFEM_MARCH_CASE(0, 8, 64)

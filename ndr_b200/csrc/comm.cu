@@ -68,6 +68,7 @@ struct NcclComm : SlabComm {
     void allreduceSum(Real *buf, size_t n, cudaStream_t s) override { VFEM_NCCL(nccl().AllReduce(buf, buf, n, ncclDouble, ncclSum, comm, s)); }
     void allreduceSumBytes(uint8_t *buf, size_t n, cudaStream_t s) override { VFEM_NCCL(nccl().AllReduce(buf, buf, n, ncclUint8, ncclSum, comm, s)); }
     bool graphSafe() const override { return graphs; }
+    bool sideStreamSafe() const override { return true; }
 };
 } // namespace
 
@@ -145,6 +146,7 @@ struct ThreadComm : SlabComm {
     void allreduceSum(Real *buf, size_t n, cudaStream_t s) override { allreduce<Real>(buf, n, s); }
     void allreduceSumBytes(uint8_t *buf, size_t n, cudaStream_t s) override { allreduce<uint8_t>(buf, n, s); }
     bool graphSafe() const override { return false; } // replaying per-rank graphs would serialise whole cycles
+    bool sideStreamSafe() const override { return false; } // the host barriers order work on the ONE shared stream only
 };
 } // namespace
 

@@ -26,6 +26,7 @@ struct SlabComm {
     virtual void allreduceSum(Real *buf, size_t n, cudaStream_t s) = 0;
     virtual void allreduceSumBytes(uint8_t *buf, size_t n, cudaStream_t s) = 0;
     virtual bool graphSafe() const = 0; // may the calls above be captured into a CUDA graph?
+    virtual bool sideStreamSafe() const = 0; // may a shift be enqueued on another stream than the solver's (overlap with compute)?
 };
 
 std::shared_ptr<SlabComm> makeNcclComm(const uint8_t *uniqueId128, int rank, int world);

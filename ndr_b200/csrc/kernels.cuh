@@ -214,10 +214,12 @@ __device__ __forceinline__ void gsNodeUpdate(const Real *t, const Real *M, unsig
 template <int N, int MODE>
 __global__ void __launch_bounds__(kBlock) applyFineKernel(Grid<N> g, K0Param<N> K, const Real *__restrict__ Ey,
                                                            const Real *__restrict__ u, const Real *__restrict__ b,
-                                                           const uint8_t *__restrict__ dmask, Real *__restrict__ out) {
+                                                           const uint8_t *__restrict__ dmask, Real *__restrict__ out, int edgeSkip) {
     int n = blockIdx.x * kBlock + threadIdx.x;
     if (n >= g.nn) return;
     int idx[N]; unflattenNode<N>(g, n, idx);
+    // the grid is a view of a larger one: rows of its first (bit 0) / last (bit 1) plane would be partial - not stored
+    if (((edgeSkip & 1) && idx[0] == 0) || ((edgeSkip & 2) && idx[0] == g.E[0])) return;
     Real acc[N];
 #pragma unroll
     for (int c = 0; c < N; ++c) acc[c] = 0.0;

@@ -147,6 +147,9 @@ MG<N>::~MG() {
     if (cublasHandle2) cublasDestroy((cublasHandle_t)cublasHandle2);
     if (factorStream) cudaStreamDestroy(factorStream);
     if (factorFork) cudaEventDestroy(factorFork);
+    if (haloStream) cudaStreamDestroy(haloStream);
+    if (haloFork) cudaEventDestroy(haloFork);
+    if (haloJoin) cudaEventDestroy(haloJoin);
     if (factorJoin) cudaEventDestroy(factorJoin);
 }
 
@@ -375,6 +378,46 @@ void MG<N>::applyMode(size_t l, const Real *u, const Real *b, Real *out) {
     VFEM_CHECK_LAUNCH(); countLaunch();
 }
 
+// Slab mode, fine level: out = op(u) with the ghost planes of u refreshed on the way.  The element layers that touch no
+// ghost plane are applied while the one-plane shifts cross NVLink on haloStream; the two layer pairs around the first and
+// last owned plane follow once the planes have landed.  Views store complete rows only (edgeSkip), so the three launches
+// write disjoint planes.
+template <int N>
+template <int MODE>
+void MG<N>::exchangeApplyFine(Real *u, const Real *b, Real *out) {
+    const Grid<N> &g = lv[0].g;
+    const int o0 = g.own0, o1 = g.own1, E0 = g.E[0];
+    const bool below = o0 > 0, above = o1 + 1 < g.n[0];
+    if (!slab() || o1 - o0 < 3 || getenv("VFEM_NO_HALO_OVERLAP")) {
+        exchange(0, u, XUP | XDOWN);
+        applyMode<MODE>(0, u, b, out);
+        return;
+    }
+    sim->moduli(); // a stale E(rho) is refreshed on the solver stream BEFORE the fork
+    cudaStream_t hs = stream;
+    if (comm->sideStreamSafe()) {
+        if (!haloStream) {
+            VFEM_CUDA(cudaStreamCreateWithFlags(&haloStream, cudaStreamNonBlocking));
+            VFEM_CUDA(cudaEventCreateWithFlags(&haloFork, cudaEventDisableTiming));
+            VFEM_CUDA(cudaEventCreateWithFlags(&haloJoin, cudaEventDisableTiming));
+        }
+        hs = haloStream;
+        VFEM_CUDA(cudaEventRecord(haloFork, stream));
+        VFEM_CUDA(cudaStreamWaitEvent(hs, haloFork, 0));
+    }
+    const size_t pd = size_t(g.ninc[0]) * N;
+    comm->shift(u + size_t(o1) * pd, below ? u + size_t(o0 - 1) * pd : u, u + size_t(o0) * pd, above ? u + size_t(o1 + 1) * pd : u, pd, true, true, hs);
+    const uint8_t *mask = maskOf(*this, 0);
+    sim->template applyFineRange<MODE>(u, b, mask, out, below ? o0 : 0, above ? o1 : E0, stream, (below ? 1 : 0) | (above ? 2 : 0));
+    // the thin boundary views follow the shift on ITS stream: they share the SMs with the tail of the interior launch
+    if (below) sim->template applyFineRange<MODE>(u, b, mask, out, o0 - 1, o0 + 1, hs, 3);
+    if (above) sim->template applyFineRange<MODE>(u, b, mask, out, o1 - 1, o1 + 1, hs, 3);
+    if (hs != stream) {
+        VFEM_CUDA(cudaEventRecord(haloJoin, hs));
+        VFEM_CUDA(cudaStreamWaitEvent(stream, haloJoin, 0));
+    }
+}
+
 template <int N> void MG<N>::applyK(size_t l, const Real *u, Real *out) { applyMode<0>(l, u, nullptr, out); }
 template <int N> void MG<N>::computeResidual(size_t l, const Real *u, const Real *b, Real *r) { applyMode<1>(l, u, b, r); }
 template <int N> void MG<N>::applyKMasked(size_t l, const Real *u, Real *out) { applyMode<2>(l, u, nullptr, out); }
@@ -465,5 +508,7 @@ template <int N> void MG<N>::zeroOutDirichlet(size_t l, Real *u) { enforceDirich
 
 template struct MG<2>;
 template struct MG<3>;
+template void MG<2>::exchangeApplyFine<0>(Real *, const Real *, Real *);
+template void MG<3>::exchangeApplyFine<0>(Real *, const Real *, Real *);
 
 } // namespace vfem

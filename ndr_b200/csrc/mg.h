@@ -42,6 +42,8 @@ struct MG : MGBase {
     void *cusolverHandle2 = nullptr, *cublasHandle2 = nullptr; // second lane of the two-ended factorisation
     cudaStream_t factorStream = nullptr;
     cudaEvent_t factorFork = nullptr, factorJoin = nullptr;
+    cudaStream_t haloStream = nullptr; // slab mode: the fine-level halo shift runs here, behind the interior K-apply
+    cudaEvent_t haloFork = nullptr, haloJoin = nullptr;
     int coarseDofs = 0;
     void *cublasHandle = nullptr;
     unsigned long long builtVersion = 0;
@@ -88,6 +90,8 @@ struct MG : MGBase {
     enum { XUP = 1, XDOWN = 2 };
     bool slab() const { return comm && comm->world > 1; }
     void exchange(size_t l, Real *v, int dirs);                 // halo planes of a level-l vector
+    // fine level: refresh the ghost planes of u AND apply the operator, the shift hidden behind the interior layers
+    template <int MODE> void exchangeApplyFine(Real *u, const Real *b, Real *out);
     void exchangeHostMask(size_t l);
     void allreduce(Real *devScalars, size_t n) { if (slab()) comm->allreduceSum(devScalars, n, stream); }
     size_t ownedOffset(size_t l) const { return size_t(lv[l].g.own0) * lv[l].g.ninc[0] * N; }

@@ -144,8 +144,7 @@ size_t MG<N>::pcg(const Real *u, const Real *b, size_t maxIter, Real tol, const 
         allreduce(sc + 0, 1);
         updateDirectionKernel<<<rb, kRedBlock, 0, stream>>>(d + off, s + off, n, sc + 0, sc + 1, first ? 1 : 0); VFEM_CHECK_LAUNCH(); countLaunch();
         first = false;
-        exchange(0, d, XUP | XDOWN);
-        applyKMasked(0, d, Ad);
+        exchangeApplyFine<2>(d, nullptr, Ad);
         dotKernel<<<rb, kRedBlock, 0, stream>>>(d + off, Ad + off, n, rw, sc + 2); VFEM_CHECK_LAUNCH(); countLaunch();
         allreduce(sc + 2, 1);
         updateSolutionKernel<<<rb, kRedBlock, 0, stream>>>(x + off, r + off, d + off, Ad + off, n, sc + 0, sc + 2, rw, sc + 3); VFEM_CHECK_LAUNCH(); countLaunch();

@@ -201,7 +201,8 @@ const Real *Sim<N>::moduli() {
 // boundary planes) receive complete rows, the two edge planes of the view partial ones.
 template <int N>
 template <int MODE>
-void Sim<N>::applyFineRange(const Real *u, const Real *b, const uint8_t *mask, Real *out, int layerLo_, int layerHi_, cudaStream_t st) {
+void Sim<N>::applyFineRange(const Real *u, const Real *b, const uint8_t *mask, Real *out, int layerLo_, int layerHi_, cudaStream_t st,
+                            int edgeSkip) {
     const Real *Ey = moduli();
     Grid<N> gv = g;
     const MarchPlan *plan = &marchPlan;
@@ -225,9 +226,10 @@ void Sim<N>::applyFineRange(const Real *u, const Real *b, const uint8_t *mask, R
         }
     }
     if (useMarch())
-        launchApplyMarch<MODE>(reinterpret_cast<const Grid<3> &>(gv), Khat, khatStructure == 2 && applyVariant != 2, *plan, Ey, u, b, mask, out, st);
+        launchApplyMarch<MODE>(reinterpret_cast<const Grid<3> &>(gv), Khat, khatStructure == 2 && applyVariant != 2, *plan, Ey, u, b, mask, out, st,
+                               edgeSkip);
     else
-        applyFineKernel<N, MODE><<<(gv.nn + kBlock - 1) / kBlock, kBlock, 0, st>>>(gv, K0, Ey, u, b, mask, out);
+        applyFineKernel<N, MODE><<<(gv.nn + kBlock - 1) / kBlock, kBlock, 0, st>>>(gv, K0, Ey, u, b, mask, out, edgeSkip);
     VFEM_CHECK_LAUNCH(); countLaunch();
 }
 
@@ -241,9 +243,8 @@ void Sim<N>::applyFine(const Real *u, const Real *b, const uint8_t *mask, Real *
 // Reference-facing call with HOST arrays (applyK(numpy) -> numpy): instead of copy-in / kernel / copy-out, the grid is cut
 // into chunks of node planes along axis 0 and the three stages are pipelined over two copy streams and the compute stream,
 // so host->device and device->host traffic overlap (PCIe is full duplex) and the kernel time disappears behind them.
-// Chunk k owns the node planes [a_k, b_k); its kernel covers the element layers [a_k - 1, b_k) and therefore also writes
-// PARTIAL rows into plane a_k - 1 (owned by chunk k-1: its copy-out must have finished) and plane b_k (rewritten,
-// complete, by chunk k+1).
+// Chunk k owns the node planes [a_k, b_k); its kernel covers the element layers [a_k - 1, b_k) and stores the complete
+// rows only (edgeSkip drops the partial planes a_k - 1 and b_k), so the chunks write disjoint planes.
 template <int N>
 void Sim<N>::applyKHost(const Real *hu, Real *hout) {
     const size_t nd = numDofs(), pd = size_t(g.ninc[0]) * N;
@@ -271,8 +272,8 @@ void Sim<N>::applyKHost(const Real *hu, Real *hout) {
     for (int k = 0; k < C; ++k) {
         const int a = bound(k), bnd = bound(k + 1);
         VFEM_CUDA(cudaStreamWaitEvent(hostComputeStream, evIn[k], 0));
-        if (k > 0) VFEM_CUDA(cudaStreamWaitEvent(hostComputeStream, evOut[k - 1], 0));
-        applyFineRange<0>(hostIn.p, nullptr, nullptr, hostOut.p, std::max(a - 1, 0), std::min(bnd, E0), hostComputeStream);
+        applyFineRange<0>(hostIn.p, nullptr, nullptr, hostOut.p, std::max(a - 1, 0), std::min(bnd, E0), hostComputeStream,
+                          (a > 0 ? 1 : 0) | (bnd < E0 ? 2 : 0));
         VFEM_CUDA(cudaEventRecord(evKernel[k], hostComputeStream));
         VFEM_CUDA(cudaStreamWaitEvent(d2hStream, evKernel[k], 0));
         VFEM_CUDA(cudaMemcpyAsync(hout + size_t(a) * pd, hostOut.p + size_t(a) * pd, size_t(bnd - a) * pd * sizeof(Real), cudaMemcpyDeviceToHost, d2hStream));
@@ -325,6 +326,9 @@ void Sim<N>::complianceGradient(const Real *u, Real *grad) {
 template struct Sim<2>;
 template struct Sim<3>;
 #define VFEM_INST(N, M) template void Sim<N>::applyFine<M>(const Real *, const Real *, const uint8_t *, Real *);
+VFEM_INST(2, 0) VFEM_INST(2, 1) VFEM_INST(2, 2) VFEM_INST(3, 0) VFEM_INST(3, 1) VFEM_INST(3, 2)
+#undef VFEM_INST
+#define VFEM_INST(N, M) template void Sim<N>::applyFineRange<M>(const Real *, const Real *, const uint8_t *, Real *, int, int, cudaStream_t, int);
 VFEM_INST(2, 0) VFEM_INST(2, 1) VFEM_INST(2, 2) VFEM_INST(3, 0) VFEM_INST(3, 1) VFEM_INST(3, 2)
 #undef VFEM_INST
 

@@ -103,7 +103,8 @@ struct Sim : SimBase {
     void applyK(const Real *u, Real *out);    // TPS.hh:905-952
     // MODE 0: K u; 1: mask(b - K u); 2: mask(K u)   (fine level; MG.hh:401-413, 719-720)
     template <int MODE> void applyFine(const Real *u, const Real *b, const uint8_t *mask, Real *out);
-    template <int MODE> void applyFineRange(const Real *u, const Real *b, const uint8_t *mask, Real *out, int layerLo, int layerHi, cudaStream_t st);
+    template <int MODE> void applyFineRange(const Real *u, const Real *b, const uint8_t *mask, Real *out, int layerLo, int layerHi, cudaStream_t st,
+                                               int edgeSkip = 0); // edgeSkip bit 0 / 1: do not store the view's first / last node plane
     void applyKHost(const Real *hu, Real *hout);  // host arrays in / out, copies pipelined with the kernel
     void complianceGradient(const Real *u, Real *g); // TPS.hh:730-751
 };

@@ -89,7 +89,8 @@ def test_slab_hierarchy_and_smoother(oracle_mod, grid, levels, world):
         nn = o.mg_level_nodes(l)
         u, b = rng.standard_normal((nn, 3)), rng.standard_normal((nn, 3))
         u = o.mg_zero_dirichlet(l, u)
-        ref[l] = (u, b, o.mg_smooth(l, u.copy(), b, True), o.mg_smooth(l, u.copy(), b, False), o.mg_residual(l, u, b), o.mg_level_dmask(l).astype(bool))
+        ref[l] = (u, b, o.mg_smooth(l, u.copy(), b, True), o.mg_smooth(l, u.copy(), b, False), o.mg_residual(l, u, b), o.mg_level_dmask(l).astype(bool),
+                  o.apply_k(u) if l == 0 else None)
     comms, hs = make_thread_comms(world), ThreadHostSum(world)
 
     def body(r):
@@ -99,7 +100,7 @@ def test_slab_hierarchy_and_smoother(oracle_mod, grid, levels, world):
         mg = s.multigrid()
         pn = s.layout.plane_nodes
         for l in range(levels):
-            u, b, uf, ub, res, dm = ref[l]
+            u, b, uf, ub, res, dm, Ku = ref[l]
             w = 1 << l
             first, last = C.c_size_t(), C.c_size_t()
             check(lib().vfem_mg_owned_planes(mg._h, l, C.byref(first), C.byref(last)))
@@ -116,6 +117,15 @@ def test_slab_hierarchy_and_smoother(oracle_mod, grid, levels, world):
                 assert rel(got[own_l], want[own_g]) < 1e-12, (l, fwd)
             got = mg.computeResidual(l, np.ascontiguousarray(u[win]), np.ascontiguousarray(b[win]))
             assert rel(got[own_l], res[own_g]) < 1e-12, l
+            if l == 0:  # ghost refresh + K-apply in one call (halo shift behind the interior layers; three disjoint views)
+                import torch
+                ul = torch.from_numpy(np.ascontiguousarray(u[win])).cuda()
+                ghost = np.ones(nloc, bool); ghost[own_l] = False
+                ul[torch.from_numpy(ghost).cuda()] = 7.0          # stale ghost planes: the call must refresh them
+                out = torch.full_like(ul, np.nan)
+                check(lib().vfem_mg_apply_k_halo(mg._h, C.c_void_p(ul.data_ptr()), C.c_void_p(out.data_ptr()), 1))
+                torch.cuda.synchronize()
+                assert rel(out.cpu().numpy()[own_l], Ku[own_g]) < 1e-13
     run_ranks(world, body)
 
 
