@@ -37,7 +37,7 @@ J = 0.5 * sl.dot(f, out)
 u = torch.randn_like(f); Ku = torch.empty_like(f)
 L = _lib.lib()
 def step():
-    _lib.check(L.vfem_mg_exchange(mg._h, 0, _dev_ptr(u, u.numel()), 1)); sl.tps.applyK(u, out=Ku)
+    _lib.check(L.vfem_mg_apply_k_halo(mg._h, _dev_ptr(u, u.numel()), _dev_ptr(Ku, Ku.numel()), 1))
 for _ in range(5): step()
 torch.cuda.synchronize(); dist.barrier()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -48,4 +48,15 @@ ms = tmax(e0.elapsed_time(e1) / 20)
 if rank == 0:
     print("compliance %.9g; K-apply + halo exchange: %.3f ms -> %.1f GDOF/s over %d GPUs (%.1f%% of %d x HBM roofline)" % (
         J, ms, 3 * nn / ms / 1e6, world, 100 * 8 * (6 * nn + grid[0] * grid[1] * grid[2]) / (ms * 1e-3) / (world * 6530.6e9), world), flush=True)
+if os.environ.get("OPS"):  # per-operator device times (collective: every rank makes the same calls)
+    import ctypes as C
+    names = {0: "GS sweep", 1: "residual", 2: "restrict", 3: "prolong", 7: "masked apply"}
+    msv = C.c_double()
+    def t(op, l, n=20):
+        _lib.check(L.vfem_mg_time_op(mg._h, op, l, n, C.byref(msv))); return msv.value * 1e3
+    for l in range(levels):
+        line = "level %d: " % l + "  ".join("%s %.1f us" % (names[o], t(o, l)) for o in (0, 1, 2, 3, 7))
+        if rank == 0: print(line, flush=True)
+    line = "coarse solve %.1f us   refresh %.1f us   FMG preconditioner pass %.1f us" % (t(4, levels), t(5, 0, 5), t(6, 0, 10))
+    if rank == 0: print(line, flush=True)
 dist.barrier(); dist.destroy_process_group()
