@@ -151,6 +151,7 @@ def our_arm(args):
     torch.cuda.set_device(local)
     _lib.check(_lib.lib().vfem_set_device(local))
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # stdout carries the JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     W, K = args.warmup, args.steps
     hbm_peak, peak_src = measured_peaks()

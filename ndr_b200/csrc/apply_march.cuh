@@ -26,6 +26,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <type_traits>
 
 namespace vfem {
 
@@ -50,6 +51,11 @@ struct MarchCfg {
     static constexpr int NT = ((RY * ZT + 31) / 32) * 32;
     static constexpr int MINB = (512 / NT) > 0 ? (512 / NT) : 1; // resident CTAs per SM the register budget is sized for
     static constexpr int XS = ZT / 32 + 2; // cross-warp slots per row
+    // running 64-bit pointers (8 more registers, ~50 fewer integer instructions per step) where the register budget has room
+    // registers per thread with MINB CTAs resident: the register file is 4 x 16384 (one bank per scheduler) and the warps are
+    // dealt round-robin, so 13-16 warps per SM stop at 128 registers and 9-12 at 168 (what __launch_bounds__ arrives at)
+    static constexpr int REGS_FIT = 16384 / (((NT / 32) * MINB + 3) / 4) / 32 / 8 * 8;
+    static constexpr bool PTR = REGS_FIT >= 160;
 };
 
 // per-thread role bits (kept in one register; tested with single-bit predicates)
@@ -141,6 +147,7 @@ __global__ void __launch_bounds__(MarchCfg<RY, ZT>::NT, MarchCfg<RY, ZT>::MINB)
 applyMarchKernel(Grid<3> g, KhatParam kh, const Real *__restrict__ Ey, const Real *__restrict__ u, const Real *__restrict__ b,
                  const uint8_t *__restrict__ dmask, Real *__restrict__ out, int XC, int edgeSkip) {
     constexpr int XS = MarchCfg<RY, ZT>::XS;
+    constexpr bool PTR = MarchCfg<RY, ZT>::PTR;
     __shared__ Real sYx[2][RY][3][ZT];   // row ry -> slot ry+1 : y-stage part for node row y+1
     __shared__ Real sX[2][RY][XS][6];    // zh of a thread whose z+1 neighbour sits in the next warp
     __shared__ Real sYsp[2][RY][3];      // y exchange of the special last-z node column
@@ -186,29 +193,37 @@ applyMarchKernel(Grid<3> g, KhatParam kh, const Real *__restrict__ Ey, const Rea
     for (int k = 0; k < 4; ++k)
 #pragma unroll
         for (int c = 0; c < 3; ++c) Gprev[k][c] = 0.0;
+    // running pointers, advanced by one plane / layer per step (no per-step 64-bit index arithmetic):
+    // uA / uB -> this thread's node of rows y / y+1 in the plane the NEXT marchFaces consumes; eP -> the modulus in Enext;
+    // oP -> this thread's output node in the plane being stored
+    const Real *uA = u + size_t(x0) * planeStride + offA, *uB = u + size_t(x0) * planeStride + offB;
+    const Real *eP = Ey + size_t(x0) * eStride + eOff;
+    Real *oP = out + (size_t(x0) * planeNodes + nodeBase) * 3;
     {
-        const Real *up = u + size_t(x0) * planeStride;
 #pragma unroll
-        for (int c = 0; c < 3; ++c) { pa[c] = up[offA + c]; pb[c] = up[offB + c]; }
-        marchFaces(pa, pb, flags, up + offA, up + offB, FA);
-        up += planeStride; // x0 + 1 <= Ex is always a valid plane
+        for (int c = 0; c < 3; ++c) { pa[c] = uA[c]; pb[c] = uB[c]; }
+        marchFaces(pa, pb, flags, uA, uB, FA);
+        uA += planeStride; uB += planeStride; // x0 + 1 <= Ex is always a valid plane
 #pragma unroll
-        for (int c = 0; c < 3; ++c) { pa[c] = up[offA + c]; pb[c] = up[offB + c]; }
-        Enext = Ey[size_t(x0) * eStride + eOff];
+        for (int c = 0; c < 3; ++c) { pa[c] = uA[c]; pb[c] = uB[c]; }
+        Enext = *eP;
     }
 
-    auto step = [&](const int it, Real (&Fold)[4][3], Real (&Fnew)[4][3]) {
+    // LAYER: the step advances through element layer x (always, except the closing step that only flushes plane Ex)
+    auto step = [&](auto hasLayer, const int it, Real (&Fold)[4][3], Real (&Fnew)[4][3]) {
+        constexpr bool LAYER = decltype(hasLayer)::value;
         const int x = x0 + it, buf = it & 1;
         Real Gtot[4][3];
-        if (x < Ex) {
-            const Real *up1 = u + size_t(x + 1) * planeStride;
-            marchFaces(pa, pb, flags, up1 + offA, up1 + offB, Fnew);
+        if (LAYER) {
+            if (!PTR) { uA = u + size_t(x + 1) * planeStride + offA; uB = u + size_t(x + 1) * planeStride + offB; }
+            marchFaces(pa, pb, flags, uA, uB, Fnew); // uA / uB: plane x + 1
             const Real Ee = (flags & MF_COL) ? Enext : 0.0;
             if (x + 2 < nx) { // prefetch the next step's inputs before the arithmetic of this one
-                const Real *up2 = up1 + planeStride;
+                if (PTR) { uA += planeStride; uB += planeStride; eP += eStride; }
+                else { uA += planeStride; uB += planeStride; eP = Ey + size_t(x + 1) * eStride + eOff; }
 #pragma unroll
-                for (int c = 0; c < 3; ++c) { pa[c] = up2[offA + c]; pb[c] = up2[offB + c]; }
-                if (x + 1 < Ex) Enext = Ey[size_t(x + 1) * eStride + eOff];
+                for (int c = 0; c < 3; ++c) { pa[c] = uA[c]; pb[c] = uB[c]; }
+                Enext = *eP;
             }
             marchLayer<SPARSE>(kh, Fold, Fnew, Ee, Gprev, Gtot);
         } else {
@@ -270,7 +285,10 @@ applyMarchKernel(Grid<3> g, KhatParam kh, const Real *__restrict__ Ey, const Rea
         }
         if (it > 0 || (flags & MF_CHUNK0)) {
             const unsigned n = unsigned(x) * planeNodes + nodeBase;
-            if (flags & MF_STORE) marchStore<MODE>(n, res, b, dmask, out);
+            if (flags & MF_STORE) {
+                if (MODE == 0 && PTR) { oP[0] = res[0]; oP[1] = res[1]; oP[2] = res[2]; }
+                else marchStore<MODE>(n, res, b, dmask, out);
+            }
             if (flags & (MF_SPSTORE | MF_TOP)) { // rare paths: last node column / last node row of the grid
                 if (flags & MF_SPSTORE) {
                     Real v[3];
@@ -296,14 +314,20 @@ applyMarchKernel(Grid<3> g, KhatParam kh, const Real *__restrict__ Ey, const Rea
                 }
             }
         }
+        if (PTR) oP += planeStride;
     };
 
     const int nIter = (x1 - x0) + ((x1 == Ex && !(edgeSkip & 2)) ? 1 : 0); // edgeSkip: the grid is a view whose first / last plane is partial
-    for (int it = 0; it < nIter; it += 2) { // two steps per trip so the face registers ping-pong without copies
-        step(it, FA, FB);
-        if (it + 1 >= nIter) break;
-        step(it + 1, FB, FA);
+    const int nLayers = x1 - x0;
+    int it = 0;
+    for (; it + 1 < nLayers; it += 2) { // two steps per trip so the face registers ping-pong without copies
+        step(std::true_type{}, it, FA, FB);
+        step(std::true_type{}, it + 1, FB, FA);
     }
+    if (it < nLayers) { // odd layer count
+        step(std::true_type{}, it, FA, FB);
+        if (nIter > nLayers) step(std::false_type{}, it + 1, FB, FA);
+    } else if (nIter > nLayers) step(std::false_type{}, it, FA, FB);
 }
 
 // tiles of t columns overlapping by one: 1 + ceil(max(0, ne - t) / (t - 1))
@@ -358,7 +382,7 @@ struct MarchPlan { int cfg = 0, XC = 2; dim3 grid; };
 // cost = waves * (steps per chunk + pipeline fill) * stepUs, with waves = CTAs / (SMs * resident CTAs per SM).
 inline MarchPlan planMarch(const Grid<3> &g, int numSMs) {
     static const int shapes[kMarchShapes][2] = {{8, 64}, {16, 32}, {15, 33}, {7, 65}, {6, 64}, {4, 64}, {8, 32}, {8, 33}, {5, 64}, {4, 33}, {6, 65}};
-    static const double stepUs[kMarchShapes] = {2.40, 2.40, 2.26, 1.90, 1.56, 2.14, 1.94, 1.55, 1.48, 1.80, 1.78};
+    static const double stepUs[kMarchShapes] = {2.40, 2.40, 2.26, 1.90, 1.42, 2.14, 1.94, 1.33, 1.30, 1.80, 1.78};
     MarchPlan best; double bestCost = 1e300;
     const char *fs = getenv("VFEM_MARCH_SHAPE"), *fx = getenv("VFEM_MARCH_XC"); // experiment overrides
     for (int s = 0; s < kMarchShapes; ++s) {

@@ -250,6 +250,7 @@ void Sim<N>::applyKHost(const Real *hu, Real *hout) {
     const size_t nd = numDofs(), pd = size_t(g.ninc[0]) * N;
     if (hostIn.n != nd) { hostIn.alloc(nd); hostOut.alloc(nd); }
     if (!h2dStream) {
+        if (const char *v = getenv("VFEM_HOST_CHUNKS")) hostChunks = std::max(1, atoi(v));
         VFEM_CUDA(cudaStreamCreateWithFlags(&h2dStream, cudaStreamNonBlocking));
         VFEM_CUDA(cudaStreamCreateWithFlags(&d2hStream, cudaStreamNonBlocking));
         VFEM_CUDA(cudaStreamCreateWithFlags(&hostComputeStream, cudaStreamNonBlocking));
@@ -262,7 +263,7 @@ void Sim<N>::applyKHost(const Real *hu, Real *hout) {
     moduli(); // refresh E(rho) on the main stream if stale, then make the side streams see it
     VFEM_CUDA(cudaStreamSynchronize(stream));
     const int E0 = g.E[0], planes = g.n[0];
-    const int C = std::max(1, std::min(kHostChunks, E0 / 4));
+    const int C = std::max(1, std::min(std::min(hostChunks, kHostChunks), E0 / 4));
     auto bound = [&](int k) { return k >= C ? planes : int((long long)E0 * k / C); }; // chunk k owns node planes [bound(k), bound(k+1))
     for (int k = 0; k < C; ++k) { // inputs: chunk k's kernel needs the node planes up to bound(k+1) inclusive
         const int p0 = k == 0 ? 0 : std::min(bound(k) + 1, planes), p1 = std::min(bound(k + 1) + 1, planes);

@@ -54,7 +54,8 @@ struct Sim : SimBase {
     int computeLo = 0;                        // first local element layer K u is evaluated on (set by the slab solver)
     std::map<int, MarchPlan> viewPlans;       // march plans of sub-grid views, keyed by their layer count
     // pipelined host-array apply (applyKHost)
-    static constexpr int kHostChunks = 4;
+    static constexpr int kHostChunks = 16; // upper bound; hostChunks are used
+    int hostChunks = 4;
     DevBuf<Real> hostIn, hostOut;
     cudaStream_t h2dStream = nullptr, d2hStream = nullptr, hostComputeStream = nullptr;
     cudaEvent_t evIn[kHostChunks] = {}, evKernel[kHostChunks] = {}, evOut[kHostChunks] = {};
