@@ -374,15 +374,15 @@ inline int computeKhat(const Real *K0 /*24x24*/, KhatParam &kh) {
     return structure;
 }
 
-constexpr int kMarchShapes = 11;
+constexpr int kMarchShapes = 13;
 struct MarchPlan { int cfg = 0, XC = 2; dim3 grid; };
 
 // Picks tile shape and chunk length from a measured cost model: a CTA advances one plane per step, and a step takes
 // stepUs[shape] on B200 whatever the chunk length (the march is latency-bound: profiles/r01d_march_shape_sweep.txt), so
 // cost = waves * (steps per chunk + pipeline fill) * stepUs, with waves = CTAs / (SMs * resident CTAs per SM).
 inline MarchPlan planMarch(const Grid<3> &g, int numSMs) {
-    static const int shapes[kMarchShapes][2] = {{8, 64}, {16, 32}, {15, 33}, {7, 65}, {6, 64}, {4, 64}, {8, 32}, {8, 33}, {5, 64}, {4, 33}, {6, 65}};
-    static const double stepUs[kMarchShapes] = {2.40, 2.40, 2.26, 1.90, 1.42, 2.14, 1.94, 1.33, 1.30, 1.80, 1.78};
+    static const int shapes[kMarchShapes][2] = {{8, 64}, {16, 32}, {15, 33}, {7, 65}, {6, 64}, {4, 64}, {8, 32}, {8, 33}, {5, 64}, {4, 33}, {6, 65}, {5, 33}, {11, 33}};
+    static const double stepUs[kMarchShapes] = {1.78, 1.90, 1.98, 1.69, 1.195, 1.68, 1.64, 1.06, 1.10, 1.66, 1.58, 1.11, 1.20}; // profiles/r01n_march_loop_sass.txt, r01q
     MarchPlan best; double bestCost = 1e300;
     const char *fs = getenv("VFEM_MARCH_SHAPE"), *fx = getenv("VFEM_MARCH_XC"); // experiment overrides
     for (int s = 0; s < kMarchShapes; ++s) {
@@ -423,6 +423,8 @@ inline void launchApplyMarch(const Grid<3> &g, const KhatParam &kh, bool sparse,
         VFEM_MARCH_CASE(8, 5, 64)
         VFEM_MARCH_CASE(9, 4, 33)
         VFEM_MARCH_CASE(10, 6, 65)
+        VFEM_MARCH_CASE(11, 5, 33)
+        VFEM_MARCH_CASE(12, 11, 33)
     }
 #undef VFEM_MARCH_CASE
 }

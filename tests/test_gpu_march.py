@@ -51,6 +51,29 @@ def test_march_matches_gather_and_oracle(oracle_mod, grid, dom):
     np.testing.assert_array_equal(a, g.applyK(u))
 
 
+@pytest.mark.parametrize("shape", range(13))
+@pytest.mark.parametrize("xc", [None, 4])
+def test_every_tile_shape(shape, xc, monkeypatch):
+    """each compiled tile shape forced through the planner overrides (several tiles along y and z, several chunks), all
+    three store modes, against the per-node gather kernel"""
+    monkeypatch.setenv("VFEM_MARCH_SHAPE", str(shape))
+    if xc:
+        monkeypatch.setenv("VFEM_MARCH_XC", str(xc))
+    from conftest import bc_path
+    grid, dom = [10, 24, 72], [1, 2, 6]
+    g, _ = make(grid, dom)
+    g.applyDisplacementsAndLoadsFromFile(bc_path("3d/cantilever_flexion.bc"))
+    info = g.applyInfo()
+    assert info["march"] == 1 and info["tile_shape"] == shape and (xc is None or info["layers_per_chunk"] == xc), info
+    rng = np.random.default_rng(shape)
+    u, b = rng.standard_normal((g.numNodes(), 3)), rng.standard_normal((g.numNodes(), 3))
+    mg = g.multigridSolver(1)
+    a, r = g.applyK(u), mg.computeResidual(0, u, b)
+    g.setApplyVariant(1)
+    assert g.applyInfo()["march"] == 0
+    assert rel(a, g.applyK(u)) < 1e-13 and rel(r, mg.computeResidual(0, u, b)) < 1e-13
+
+
 def test_march_residual_and_masked_modes(oracle_mod):
     """MODE 1 (mask(b - K u)) and MODE 2 (mask(K u)) through MultigridSolver.computeResidual / PCG's A d."""
     import ndr_b200.pyVoxelFEM as V

@@ -10,7 +10,7 @@ import ndr_b200.pyVoxelFEM as V
 grid = [int(a) for a in sys.argv[1:4]] if len(sys.argv) >= 4 else [128, 64, 64]
 peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
 MAT = os.path.join(ROOT, "tests", "golden", "fixtures", "materials", "B9Creator.material")
-shapes = {0: (8, 64), 1: (16, 32), 2: (15, 33), 3: (7, 65), 4: (6, 64), 5: (4, 64), 6: (8, 32), 7: (8, 33), 8: (5, 64), 9: (4, 33), 10: (6, 65)}
+shapes = {0: (8, 64), 1: (16, 32), 2: (15, 33), 3: (7, 65), 4: (6, 64), 5: (4, 64), 6: (8, 32), 7: (8, 33), 8: (5, 64), 9: (4, 33), 10: (6, 65), 11: (5, 33), 12: (11, 33)}
 cases = [(None, None)] + [(s, None) for s in shapes] + [(0, x) for x in (5, 9, 17, 33)] + [(4, x) for x in (7, 9, 13)] + [(5, x) for x in (5, 9, 13)]
 if os.environ.get("SWEEP_SHORT"): cases = [(0, None), (4, None), (5, None), (3, None)]
 if os.environ.get("SWEEP_CASES"): cases = [tuple(None if v == "-" else int(v) for v in c.split(":")) for c in os.environ["SWEEP_CASES"].split(",")]
