@@ -184,6 +184,9 @@ applyMarchKernel(Grid<3> g, KhatParam kh, const Real *__restrict__ Ey, const Rea
         nodeBase = unsigned(yc * nz + zc);
         sIdx = unsigned(ry * 3 * ZT + tx);
     }
+    // opaque to the optimiser: otherwise it re-derives single role bits from threadIdx / blockIdx inside the march loop
+    // (~25 integer instructions per step) instead of testing the register
+    asm volatile("" : "+r"(flags), "+r"(sIdx));
     const Real prevMask = (flags & MF_PREV) ? 1.0 : 0.0;
     const unsigned planeStride = unsigned(ny) * unsigned(nz) * 3u, planeNodes = unsigned(ny) * unsigned(nz);
     const unsigned eStride = unsigned(g.E[1]) * unsigned(g.E[2]);
