@@ -334,11 +334,24 @@ void MG<N>::coarseSolve(const Real *b, Real *x) {
         const size_t smem = size_t(4) * coarseP * sizeof(Real);
         ChainIdx ci{coarsePlanes, coarseMid};
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(kChainCluster); cfg.blockDim = dim3(kChainThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = kChainCluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.blockDim = dim3(kChainThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
         cfg.attrs = attr; cfg.numAttrs = 1;
+        if (chainCluster == 0) { // 16 CTAs (non-portable size) halve the matrix rows per SM and step; 8 where that does not fit
+            chainCluster = kChainCluster;
+            const char *v = getenv("VFEM_CHAIN_CLUSTER");
+            const int want = v ? atoi(v) : 16;
+            if (want > kChainCluster && want <= 16 &&
+                cudaFuncSetAttribute(blockTriChainKernel<N>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
+                cfg.gridDim = dim3(want); attr[0].val.clusterDim.x = want;
+                int n = 0;
+                if (cudaOccupancyMaxActiveClusters(&n, blockTriChainKernel<N>, &cfg) == cudaSuccess && n >= 1) chainCluster = want;
+            } else if (want >= 1 && want < kChainCluster && 2 * coarseP <= kChainSlots * want * (kChainThreads / 32)) chainCluster = want;
+            (void)cudaGetLastError();
+        }
+        cfg.gridDim = dim3(chainCluster); attr[0].val.clusterDim.x = chainCluster;
         VFEM_CUDA(cudaLaunchKernelEx(&cfg, blockTriChainKernel<N>, coarseP, ci, (const Real *)d_Trm.p, (const Real *)d_Tcm.p,
                                      (const Real *)d_Sinv.p, b, cmask, x, d_z.p));
     } else { // large planes: the whole device, one grid barrier per chain step

@@ -113,6 +113,7 @@ struct MG : MGBase {
     void smoothColoured(size_t l, Real *u, const Real *b, bool forward);               // MG.hh:336-340
     void smooth(size_t l, Real *u, const Real *b, bool forward, size_t sweeps);        // `sweeps` x smoothColoured, fused on the assembled levels
     int sweepGridBlocks = 0, chainGridBlocks = 0;        // co-resident blocks of gsStencilSweepKernel (cooperative launch)
+    int chainCluster = 0;                                // CTAs of the cluster chain kernel (chosen at the first coarse solve)
     void restriction(size_t lf, const Real *vf, Real *bc);                             // MG.hh:145-180
     void interpolate(size_t lf, const Real *xc, Real *xf, bool accumulate);            // MG.hh:115-141
     void zeroOutDirichlet(size_t l, Real *u);                                          // MG.hh:364-378
