@@ -128,7 +128,7 @@ def reference_arm(args, rank):
             "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "3D cantilever 128x64x64 Q1 hex, matrix-free K(rho)u, seed-88 densities"},
             "cpu_baseline": cb, "e2e": {"value": val, "unit": "GDOF/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def layer_densities(layer_lo, layer_hi, plane_elems):
@@ -151,7 +151,6 @@ def our_arm(args):
     torch.cuda.set_device(local)
     _lib.check(_lib.lib().vfem_set_device(local))
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # stdout carries the JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     W, K = args.warmup, args.steps
     hbm_peak, peak_src = measured_peaks()
@@ -277,7 +276,7 @@ def our_arm(args):
         line["solve"] = solve
     if cpu:
         line["cpu_baseline"] = cpu
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.barrier(); dist.destroy_process_group()
 
@@ -319,7 +318,24 @@ def time_solve(V, torch, args, g, mg, world, dist, reps=5):
     return res
 
 
+_JSON_FD = None
+
+
+def emit(line):
+    """the ONE JSON line, on the process's real stdout"""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    # stdout carries the JSON line only: whatever libraries print there (NCCL's version banner, ...) goes to stderr
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
