@@ -340,14 +340,14 @@ inline int marchTiles(int ne, int t) { return 1 + (ne > t ? (ne - t + t - 2) / (
 // basis (use the gather kernel), 1 = block diagonal (dense 3x3 blocks), 2 = block diagonal with the
 // isotropic sparsity pattern of khatEntryNonZero.
 inline int computeKhat(const Real *K0 /*24x24*/, KhatParam &kh) {
-    static Real W[24][24];
+    Real W[24][24]; // locals: simulators are built concurrently by the slab tests' rank threads
     for (int m = 0; m < 8; ++m)
         for (int j = 0; j < 8; ++j) {
             const int pc = khatPopc(m & j);
             for (int c = 0; c < 3; ++c)
                 for (int c2 = 0; c2 < 3; ++c2) W[m * 3 + c][j * 3 + c2] = (c == c2) ? ((pc & 1) ? -1.0 : 1.0) : 0.0;
         }
-    static Real T[24][24], Kh[24][24];
+    Real T[24][24], Kh[24][24];
     Real kmax = 0.0;
     for (int a = 0; a < 24; ++a)
         for (int j = 0; j < 24; ++j) {

@@ -26,3 +26,9 @@ def oracle_mod():
     from oracle import oracle as O
     O.build()
     return O
+
+
+def pytest_collection_modifyitems(config, items):
+    """The multi-rank-on-one-GPU slab tests run last: they are the longest and the only ones that drive several host
+    threads, so `-x` still gets through the single-rank parity tests first."""
+    items.sort(key=lambda it: 1 if "test_gpu_slab" in it.nodeid else 0)
