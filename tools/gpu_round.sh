@@ -10,7 +10,7 @@ timeout 300 python __graft_entry__.py --smoke > $O/smoke.log 2>&1; echo "smoke r
 timeout 600 python bench.py > $O/bench.json 2> $O/bench.err; echo "bench rc=$?" | tee -a $O/bench.err
 timeout 300 python bench.py --impl reference --steps 20 --warmup 3 > $O/bench_ref.json 2> $O/bench_ref.err
 SWEEP_CASES="-:-,4:-,0:-,3:-" timeout 600 python tools/march_sweep.py 128 64 64 > $O/sweep_128.log 2>&1
-SWEEP_CASES="-:-,3:-" timeout 600 python tools/march_sweep.py 256 128 128 > $O/sweep_256.log 2>&1
+SWEEP_CASES="-:-,3:-,12:-,11:-" timeout 600 python tools/march_sweep.py 256 128 128 > $O/sweep_256.log 2>&1
 REPS=3 timeout 600 python tools/solve_profile.py 128 64 64 3 > $O/solve_128.log 2>&1
 REPS=3 timeout 600 python tools/solve_profile.py 256 128 128 3 > $O/solve_256.log 2>&1
 # ncu: launch list of the bench command, then the K-apply kernel in full
