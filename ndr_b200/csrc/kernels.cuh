@@ -255,6 +255,91 @@ __global__ void __launch_bounds__(kBlock, MINB) gsFineKernel(Grid<N> g, K0Param<
 }
 
 
+// Split form of the 3-D fine-level colour phase: a CTA of 8 warps updates 32 colour nodes, warp S computes the
+// contribution of incident element slot S of every node (8 nodes x 3 loads, 72 DFMA with K0 entries as constant-bank
+// operands, since S is a compile-time constant of the warp's code path), the 8 partial rows and diagonal blocks are
+// summed through shared memory in slot order (fixed order => bit-reproducible) and warp 0 does the node update.
+// One thread per node (gsFineKernel) holds the whole 27-node neighbourhood in registers (150 registers, 17 %
+// occupancy, 3 dependent FMA chains): 8x the threads at a third of the registers hide the FP64 latency instead.
+template <int S>
+__device__ __forceinline__ void gsSplitSlot(const Grid<3> &g, const K0Param<3> &K, const Real *__restrict__ Ey, const Real *u,
+                                            const int *idx, Real *part /*[12]: row (3), M (9)*/) {
+    constexpr int KS = 24;
+    constexpr int s0 = (S >> 2) & 1, s1 = (S >> 1) & 1, s2 = S & 1;
+    constexpr int loc = ((1 - s0) << 2) | ((1 - s1) << 1) | (1 - s2);
+    const int e0 = idx[0] - 1 + s0, e1 = idx[1] - 1 + s1, e2 = idx[2] - 1 + s2;
+    const bool ok = e0 >= 0 && e0 < g.E[0] && e1 >= 0 && e1 < g.E[1] && e2 >= 0 && e2 < g.E[2];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) part[i] = 0.0;
+    if (!ok) return;
+    const Real Ee = Ey[e0 * g.einc[0] + e1 * g.einc[1] + e2];
+    const Real *ue = u + size_t(e0 * g.ninc[0] + e1 * g.ninc[1] + e2) * 3;
+    Real ra[3] = {0.0, 0.0, 0.0}, rb[3] = {0.0, 0.0, 0.0}; // two half sums: 6 independent FMA chains
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        const Real *p = ue + size_t(((q >> 2) & 1) * g.ninc[0] + ((q >> 1) & 1) * g.ninc[1] + (q & 1)) * 3;
+        const Real v0 = p[0], v1 = p[1], v2 = p[2];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            Real &r = (q < 4) ? ra[c] : rb[c];
+            r = fma(K.k[(loc * 3 + c) * KS + q * 3 + 0], v0, r);
+            r = fma(K.k[(loc * 3 + c) * KS + q * 3 + 1], v1, r);
+            r = fma(K.k[(loc * 3 + c) * KS + q * 3 + 2], v2, r);
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) part[c] = Ee * (ra[c] + rb[c]);
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int c2 = 0; c2 < 3; ++c2) part[3 + c * 3 + c2] = Ee * K.k[(loc * 3 + c) * KS + loc * 3 + c2];
+}
+
+constexpr int kGsSplitNodes = 32;
+static __global__ void __launch_bounds__(256, 3) gsFineSplitKernel(Grid<3> g, K0Param<3> K, const Real *__restrict__ Ey, Real *u,
+                                                            const Real *__restrict__ b, const uint8_t *__restrict__ dmask, int colour,
+                                                            int forward) {
+    __shared__ Real sPart[8][12][kGsSplitNodes];
+    __shared__ Real sSum[12][kGsSplitNodes];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int idx[3];
+    const bool valid = colourNode<3>(g, blockIdx.x * kGsSplitNodes + lane, colour, idx);
+    Real part[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) part[i] = 0.0;
+    if (valid) {
+        switch (w) { // warp-uniform
+        case 0: gsSplitSlot<0>(g, K, Ey, u, idx, part); break;
+        case 1: gsSplitSlot<1>(g, K, Ey, u, idx, part); break;
+        case 2: gsSplitSlot<2>(g, K, Ey, u, idx, part); break;
+        case 3: gsSplitSlot<3>(g, K, Ey, u, idx, part); break;
+        case 4: gsSplitSlot<4>(g, K, Ey, u, idx, part); break;
+        case 5: gsSplitSlot<5>(g, K, Ey, u, idx, part); break;
+        case 6: gsSplitSlot<6>(g, K, Ey, u, idx, part); break;
+        default: gsSplitSlot<7>(g, K, Ey, u, idx, part); break;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 12; ++i) sPart[w][i][lane] = part[i];
+    __syncthreads();
+    for (int i = w; i < 12; i += 8) { // slot order 0..7, as the one-thread form sums them
+        Real s = sPart[0][i][lane];
+#pragma unroll
+        for (int k = 1; k < 8; ++k) s += sPart[k][i][lane];
+        sSum[i][lane] = s;
+    }
+    __syncthreads();
+    if (w == 0 && valid) {
+        const int n = flattenNode<3>(g, idx);
+        Real tt[3], M[9];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) tt[c] = b[size_t(n) * 3 + c] - sSum[c][lane];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) M[i] = sSum[3 + i][lane];
+        gsNodeUpdate<3>(tt, M, dmask[n], forward != 0, u, n);
+    }
+}
+
 // ---- warp-per-node kernels for the assembled levels: persistent warps striding over the nodes ----
 constexpr int kWarpBlock = 256; // 8 warps per block
 inline unsigned warpGridBlocks(long long nodes) {
@@ -319,7 +404,7 @@ __global__ void __launch_bounds__(kWarpBlock) gsStencilWarpKernel(Grid<N> g, con
 // small assembled levels are otherwise pure launch latency).  u is read with ld.global.cg: other SMs rewrite it between
 // the phases.  [q0, q1) selects the part of the sequence to run (the slab solver splits a sweep at its halo exchanges).
 template <int N>
-__global__ void __launch_bounds__(kWarpBlock) gsStencilSweepKernel(Grid<N> g, const Real *__restrict__ S, Real *u, const Real *__restrict__ b,
+__global__ void __launch_bounds__(kWarpBlock, 2) gsStencilSweepKernel(Grid<N> g, const Real *__restrict__ S, Real *u, const Real *__restrict__ b,
                                                                     const uint8_t *__restrict__ dmask, int forward, int q0, int q1) {
     constexpr int NST = ipow3(N), NN = N * N, NPE = 1 << N;
     namespace cg = cooperative_groups;
@@ -329,29 +414,65 @@ __global__ void __launch_bounds__(kWarpBlock) gsStencilSweepKernel(Grid<N> g, co
     for (int q = q0; q < q1; ++q) {
         const int colour = forward ? (q % NPE) : (NPE - 1 - q % NPE);
         const int count = colourCount<N>(g, colour);
-        for (int t = (blockIdx.x * kWarpBlock + threadIdx.x) >> 5; t < count; t += nwarps) {
+        // software pipeline over the warp's nodes of this colour: the loads of node t + nwarps are issued before the
+        // reduction / substitution of node t (same-colour nodes are not neighbours, so u read ahead inside a phase is current)
+        constexpr int ROW = StencilLane<N>::ROW, J = StencilLane<N>::J;
+        struct Slot { Real Sv[N][J], uv[J], bv; unsigned mask; int n; }; // bv: lanes 0..N-1 hold b[n][lane]; lane 0 holds the mask
+        auto load = [&](int t, Slot &L) {
             int idx[N];
             colourNode<N>(g, t, colour, idx);
-            const int n = flattenNode<N>(g, idx);
-            Real M[NN], tt[N];
-            unsigned mask = 0;
-            if (lane == 0) {
+            L.n = flattenNode<N>(g, idx);
+            const Real *Sn = S + size_t(L.n) * N * ROW + lane;
 #pragma unroll
-                for (int i = 0; i < NN; ++i) M[i] = S[stencilIndex<N>(n, NST / 2, i)];
+            for (int j = 0; j < J; ++j) {
+                const int a = min(max(L.n * N + sl.uoff[j], 0), g.nn * N - 1);
+                L.uv[j] = sl.valid[j] ? __ldcg(u + a) : 0.0;
 #pragma unroll
-                for (int c = 0; c < N; ++c) tt[c] = b[size_t(n) * N + c];
-                mask = dmask[n];
+                for (int r = 0; r < N; ++r) L.Sv[r][j] = sl.valid[j] ? Sn[r * ROW + 32 * j] : 0.0;
             }
+            L.bv = (lane < N) ? b[size_t(L.n) * N + lane] : 0.0;
+            L.mask = (lane == 0) ? unsigned(dmask[L.n]) : 0u;
+        };
+        int t = (blockIdx.x * kWarpBlock + threadIdx.x) >> 5;
+        Slot cur;
+        if (t < count) load(t, cur);
+        while (t < count) {
+            const int tn = t + nwarps;
+            Slot nxt;
+            if (tn < count) load(tn, nxt);
             Real acc[N];
-            stencilWarpRow<N, true>(sl, g.nn * N, S, u, n, lane, acc);
-            if (lane == 0) {
 #pragma unroll
-                for (int c = 0; c < N; ++c) tt[c] -= acc[c];
-                Real du[N];
-                if (forward) gsNodeSubst<N, true>(tt, M, mask, du); else gsNodeSubst<N, false>(tt, M, mask, du);
+            for (int r = 0; r < N; ++r) {
+                Real s = 0.0;
 #pragma unroll
-                for (int c = 0; c < N; ++c) u[size_t(n) * N + c] = __ldcg(u + size_t(n) * N + c) + du[c];
+                for (int j = 0; j < J; ++j)
+                    if (sl.valid[j]) s = fma(cur.Sv[r][j], cur.uv[j], s);
+                acc[r] = s;
             }
+#pragma unroll
+            for (int r = 0; r < N; ++r)
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) acc[r] += __shfl_xor_sync(0xffffffffu, acc[r], o);
+            // the diagonal block is part of the rows the lanes already hold (entries (NST/2)*N + c of each row)
+            Real M[NN], tt[N];
+#pragma unroll
+            for (int r = 0; r < N; ++r)
+#pragma unroll
+                for (int c = 0; c < N; ++c) {
+                    constexpr int e0 = (NST / 2) * N;
+                    const int e = e0 + c;
+                    M[r * N + c] = __shfl_sync(0xffffffffu, cur.Sv[r][e / 32], e % 32);
+                }
+#pragma unroll
+            for (int c = 0; c < N; ++c) tt[c] = __shfl_sync(0xffffffffu, cur.bv, c) - acc[c];
+            if (lane == 0) {
+                Real du[N];
+                if (forward) gsNodeSubst<N, true>(tt, M, cur.mask, du); else gsNodeSubst<N, false>(tt, M, cur.mask, du);
+#pragma unroll
+                for (int c = 0; c < N; ++c) u[size_t(cur.n) * N + c] = __ldcg(u + size_t(cur.n) * N + c) + du[c];
+            }
+            if (tn < count) cur = nxt;
+            t = tn;
         }
         if (q + 1 < q1) grid.sync();
     }
