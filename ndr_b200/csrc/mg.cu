@@ -436,9 +436,11 @@ template <int N> void MG<N>::applyK(size_t l, const Real *u, Real *out) { applyM
 template <int N> void MG<N>::computeResidual(size_t l, const Real *u, const Real *b, Real *r) { applyMode<1>(l, u, b, r); }
 template <int N> void MG<N>::applyKMasked(size_t l, const Real *u, Real *out) { applyMode<2>(l, u, nullptr, out); }
 
-// 3-D only (the 2-D fine level keeps the one-thread-per-node form)
+// 3-D only (the 2-D fine level keeps the one-thread-per-node form); variant 8 = split kernel, 16 = 16-byte gather loads
+static int gsVariantGlobal = 4;
 static inline void launchGsFineSplit(const Grid<3> &g, const K0Param<3> &K, const Real *Ey, Real *u, const Real *b, const uint8_t *dmask,
                                      int colour, int forward, int cnt, cudaStream_t stream) {
+    if (gsVariantGlobal >= 16) { gsFineVecKernel<2><<<unsigned((cnt + kBlock - 1) / kBlock), kBlock, 0, stream>>>(g, K, Ey, u, b, dmask, colour, forward); return; }
     gsFineSplitKernel<<<unsigned((cnt + kGsSplitNodes - 1) / kGsSplitNodes), 256, 0, stream>>>(g, K, Ey, u, b, dmask, colour, forward);
 }
 static inline void launchGsFineSplit(const Grid<2> &, const K0Param<2> &, const Real *, Real *, const Real *, const uint8_t *, int, int, int,
@@ -458,6 +460,7 @@ void MG<N>::smoothColoured(size_t l, Real *u, const Real *b, bool forward) {
         if (cnt > 0) {
             const unsigned blocks = unsigned((cnt + kBlock - 1) / kBlock);
             if (l == 0) {
+                if (N == 3 && gsVariant >= 8) gsVariantGlobal = gsVariant;
                 if (N == 3 && gsVariant >= 8) launchGsFineSplit(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0, cnt, stream);
                 else if (gsVariant == 4) gsFineKernel<N, 4><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
                 else if (gsVariant == 3) gsFineKernel<N, 3><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
