@@ -74,47 +74,68 @@ def algorithmic_bytes(nn, ne, N=3):
     return 8 * (2 * N * nn + ne)  # read u, write K u, read E(rho)   
 
 
-def run_cpu_kapply(budget_s, threads=None, solve=True):
-    """CPU restatement of the reference (oracle/): K-apply GDOF/s on the bench grid + one MG-PCG solve."""
+def host_threads():
+    """physical cores of this box (the reference sizes TBB the same way, training/train_voxelfem.py:38); torchrun exports
+    OMP_NUM_THREADS=1, so the oracle's thread count is always set explicitly"""
+    try:
+        import psutil
+        n = psutil.cpu_count(logical=False)
+    except Exception:  # noqa: BLE001
+        n = None
+    return int(n or os.cpu_count() or 1)
+
+
+def oracle_sim(grid, domain, rho):
     from oracle import oracle as O
     O.build()
-    if threads:
-        O.set_num_threads(threads)
-    s = O.OracleSim([0, 0, 0], DOMAIN, GRID)
+    O.set_num_threads(host_threads())
+    s = O.OracleSim([0, 0, 0], domain, grid)
     s.read_material(MATERIAL)
-    s.set_densities(np.random.default_rng(88).uniform(0, 1, s.ne))
+    s.set_densities(rho)
     s.apply_bc_file(BC)
     s.set_simp(1.0, 1e-4, 3.0)
+    return O, s
+
+
+def run_cpu_kapply(budget_s, solve=True):
+    """CPU restatement of the reference (oracle/): K-apply GDOF/s on the bench grid + one MG-PCG solve (kept for the parity block)."""
+    O, s = oracle_sim(GRID, DOMAIN, np.random.default_rng(88).uniform(0, 1, int(np.prod(GRID))))
     u = np.random.default_rng(89).standard_normal((s.nn, 3))
-    s.apply_k(u)
+    for _ in range(10):
+        s.apply_k(u)
     t0, reps = time.perf_counter(), 0
     while reps < 3 or (time.perf_counter() - t0 < budget_s and reps < 200):
         s.apply_k(u); reps += 1
     dt = (time.perf_counter() - t0) / reps
     out = {"value": 3 * s.nn / dt / 1e9, "unit": "GDOF/s", "cores": O.max_threads(), "kind": "port",
-           "sample": "%d K-applies of the 128x64x64 cantilever (seed-88 densities), OpenMP oracle restatement; the reference binary is "
-                     "unbuildable here (Eigen/TBB/SuiteSparse absent)" % reps, "ms_per_apply": dt * 1e3}
+           "sample": "%d K-applies of the 128x64x64 cantilever (seed-88 densities) after 10 warm-up applies, OpenMP oracle restatement; the "
+                     "reference binary is unbuildable here (Eigen/TBB/SuiteSparse absent)" % reps, "ms_per_apply": dt * 1e3}
+    sol = None
     if solve:
         s.mg_create(3)
         f = s.load_vector()
         t0 = time.perf_counter()
-        _, its, _ = s.mg_pcg(np.zeros_like(f), f, 100, 1e-4, 1, 2, True)
+        x, its, hist = s.mg_pcg(np.zeros_like(f), f, 100, 1e-4, 1, 2, True)
         out["solve_ms"] = (time.perf_counter() - t0) * 1e3
         out["solve_iterations"] = int(its)
-    return out
+        sol = {"u": x, "f": f, "iterations": int(its), "residual": float(hist[-1]) if len(hist) else None}
+    return out, sol
 
 
 def reference_arm(args, rank):
+    """The reference's CPU algorithm (oracle restatement; the reference binary is unbuildable here) on all physical host
+    cores, on the SAME workload as our arm at this --gpus: the (gpus*128)x64x64 grid with the same densities."""
     if rank != 0:
         return
-    W, K = args.warmup, args.steps
-    from oracle import oracle as O
-    O.build()
-    s = O.OracleSim([0, 0, 0], DOMAIN, GRID)
-    s.read_material(MATERIAL)
-    s.set_densities(np.random.default_rng(88).uniform(0, 1, s.ne))
-    s.set_simp(1.0, 1e-4, 3.0)
+    W, K, world = args.warmup, args.steps, args.gpus
+    gE = [GRID[0] * world, GRID[1], GRID[2]]
+    dom = [DOMAIN[0] * world, DOMAIN[1], DOMAIN[2]]
+    rho = np.random.default_rng(88).uniform(0, 1, int(np.prod(gE))) if world == 1 else layer_densities(0, gE[0], GRID[1] * GRID[2])
+    O, s = oracle_sim(gE, dom, rho)
     u = np.random.default_rng(89).standard_normal((s.nn, 3))
+    t_pre, pre = time.perf_counter(), 0
+    while pre < 50 and time.perf_counter() - t_pre < 20.0:  # steady state (page faults, thread pool, caches) before the W warm-up steps
+        s.apply_k(u); pre += 1
     for _ in range(W):
         s.apply_k(u)
     t0 = time.perf_counter()
@@ -123,12 +144,23 @@ def reference_arm(args, rank):
     dt = (time.perf_counter() - t0) / K
     val = 3 * s.nn / dt / 1e9
     cb = {"value": val, "unit": "GDOF/s", "cores": O.max_threads(), "kind": "port",
-          "sample": "%d K-applies, 128x64x64 cantilever, OpenMP restatement of the reference algorithm (reference unbuildable here)" % K}
+          "sample": "%d K-applies (after %d + %d warm-up applies) of the %dx%dx%d cantilever, OpenMP restatement of the reference algorithm "
+                    "(reference unbuildable here)" % (K, pre, W, gE[0], gE[1], gE[2])}
     line = {"impl": "reference", "metric": "k_apply_gdof_per_s", "value": val, "unit": "GDOF/s", "n_gpus": args.gpus, "steps": K, "warmup": W,
             "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "3D cantilever 128x64x64 Q1 hex, matrix-free K(rho)u, seed-88 densities"},
+            "config": workload_config(gE, world, None, None),
             "cpu_baseline": cb, "e2e": {"value": val, "unit": "GDOF/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     emit(line)
+
+
+def workload_config(gE, world, nsets, nn_l):
+    cfg = {"workload": "3D cantilever %dx%dx%d Q1 hex (128x64x64 element layers per GPU, slabs along axis 0), matrix-free K(rho)u, "
+                       "seed-88 uniform(0,1) densities, E_min=1e-4, p=3" % tuple(gE),
+           "dofs": 3 * (gE[0] + 1) * (gE[1] + 1) * (gE[2] + 1)}
+    if nsets:
+        cfg["l2"] = "ring of %d u/Ku buffer pairs (%.0f MB) > 126 MB L2" % (nsets, nsets * 48 * nn_l / 1e6)
+        cfg["halo"] = "none" if world == 1 else "1 node plane (%d B) per interior face per apply, ncclSend/ncclRecv on the solver stream" % ((gE[1] + 1) * (gE[2] + 1) * 24)
+    return cfg
 
 
 def layer_densities(layer_lo, layer_hi, plane_elems):
@@ -137,13 +169,137 @@ def layer_densities(layer_lo, layer_hi, plane_elems):
     return np.concatenate([np.random.default_rng([88, k]).uniform(0, 1, plane_elems) for k in range(layer_lo, layer_hi)])
 
 
+def _ring(tensors):
+    import ctypes as C
+    return (C.c_void_p * len(tensors))(*[t.data_ptr() for t in tensors])
+
+
+class Workload:
+    """one grid on `world` ranks: simulator (+ slab solver for world > 1), multigrid hierarchy, load vector"""
+
+    def __init__(self, V, S, torch, dist, gE, dom, bc, levels, rank, world, local, rho_mode):
+        self.gE, self.world, self.levels = gE, world, levels
+        bbmin, bbmax = np.zeros(3), np.array(dom, float)
+        plane = gE[1] * gE[2]
+        if world == 1:
+            tps = V.TensorProductSimulator([1, 1, 1], [bbmin, bbmax], gE)
+            tps.readMaterial(MATERIAL)
+            tps.setElementDensities(np.random.default_rng(88).uniform(0, 1, tps.numElements()) if rho_mode == "flat" else layer_densities(0, gE[0], plane))
+            tps.applyDisplacementsAndLoadsFromFile(bc)
+            tps.E_0, tps.E_min, tps.gamma = 1.0, 1e-4, 3.0
+            self.mg = tps.multigridSolver(levels)
+            self.mg_halo = None
+        else:
+            comm = S.make_nccl_comm(dist, rank, world)
+            sl = S.SlabSolver(gE, bbmin, bbmax, levels, rank, world, comm, S.dist_host_sum(dist, torch.device("cuda", local)), MATERIAL)
+            tps, lay = sl.tps, sl.layout
+            tps.setElementDensities(layer_densities(lay.layer_lo, lay.layer_hi, lay.plane_elems))
+            sl.apply_bc_file(bc)
+            tps.E_0, tps.E_min, tps.gamma = 1.0, 1e-4, 3.0
+            self.mg = sl.multigrid()
+            self.mg_halo = self.mg._h
+            self.slab = sl
+        self.tps = tps
+        self.nn_l, self.ne_l = tps.numNodes(), tps.numElements()
+        self.nn_global = (gE[0] + 1) * (gE[1] + 1) * (gE[2] + 1)
+        self.ne_global = gE[0] * gE[1] * gE[2]
+
+
+def time_kapply(L, torch, dist, wl, W, K, seed, preheat_s=0.3):
+    """K matrix-free applies (N > 1: + the one-plane halo shift per interior face, hidden behind the interior layers) issued by ONE
+    C-ABI call, so the Python launch rate is outside the timed region; CUDA events on the library's stream (the legacy default
+    stream, which is also torch's current stream here); max over ranks.  Returns (ms total over K steps, ms per kernel alone, launches)."""
+    world = wl.world
+    nsets = max(2, int(np.ceil(2.5 * L2_BYTES / (16 * 3 * wl.nn_l))))  # ring of u/Ku pairs larger than L2
+    gen = torch.Generator(device="cuda"); gen.manual_seed(seed)
+    us = [torch.randn(wl.nn_l, 3, dtype=torch.float64, device="cuda", generator=gen) for _ in range(nsets)]
+    outs = [torch.zeros(wl.nn_l, 3, dtype=torch.float64, device="cuda") for _ in range(nsets)]
+    pu, po = _ring(us), _ring(outs)
+
+    def run(start, count, halo=True):
+        if wl.mg_halo and halo:
+            _lib_check(L.vfem_mg_apply_k_halo_ring(wl.mg_halo, pu, po, nsets, start, count))
+        else:
+            _lib_check(L.vfem_tps_apply_k_ring(wl.tps._h, pu, po, nsets, start, count))
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # untimed: every ring buffer touched, clocks ramped to their load state, then the W warm-up steps
+    # (a fixed count derived from the GLOBAL size: the ranks must issue the same number of collective applies)
+    reps = max(1, min(500, int(preheat_s / (nsets * 3.0 * wl.nn_global / world / 60e9))))
+    for _ in range(reps):
+        run(0, nsets)
+    run(0, W)
+    sync_all()
+    launches0 = L.vfem_launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    run(W, K)
+    ev1.record()
+    sync_all()
+    ms = ev0.elapsed_time(ev1)
+    launches = L.vfem_launch_count() - launches0
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    # the dominant kernel alone (local apply, no halo exchange): the roofline leg
+    torch.cuda.synchronize()
+    ev0.record()
+    run(W, K, halo=False)
+    ev1.record(); torch.cuda.synchronize()
+    kms = ev0.elapsed_time(ev1) / K
+    return ms, kms, int(launches), nsets, (us, outs)
+
+
+MARCH_SHAPES = [(8, 64), (16, 32), (15, 33), (7, 65), (6, 64), (4, 64), (8, 32), (8, 33), (5, 64), (4, 33), (6, 65), (5, 33), (11, 33)]
+
+
+def kernel_label(tps):
+    info = tps.applyInfo()
+    if not info["march"]:
+        return "applyFineKernel<3,0> (per-node gather)"
+    ry, zt = MARCH_SHAPES[info["tile_shape"]] if info["tile_shape"] < len(MARCH_SHAPES) else (0, 0)
+    return "applyMarchKernel<MODE=0, SPARSE=%s, RY=%d, ZT=%d> grid (%d,%d,%d), %d layers per chunk" % (
+        "true" if info["k0_structure"] == 2 else "false", ry, zt, info["grid_x"], info["grid_y"], info["grid_z"], info["layers_per_chunk"])
+
+
+def roofline_block(wl, kms, hbm_peak, peak_src):
+    set_bytes = algorithmic_bytes(wl.nn_l, wl.ne_l)
+    achieved = set_bytes / (kms * 1e-3) / 1e9
+    r = {"bound": "hbm", "kernel": kernel_label(wl.tps), "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+         "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": set_bytes, "kernel_ms": kms,
+         "gdof_per_s_per_gpu": 3.0 * wl.nn_l / (kms * 1e-3) / 1e9}
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):  # dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture, keyed by grid and kernel source
+        t = json.load(open(tp))
+        key = "%dx%dx%d" % tuple(wl.gE)
+        ent = t.get("apply_march", {}).get(key)
+        if ent and ent.get("kernel_source_sha16") == kernel_source_sha():
+            r["traffic"] = ent["dram_bytes_per_launch"]
+            r["traffic_source"] = ent.get("source")
+    return r
+
+
+def kernel_source_sha():
+    import hashlib
+    return hashlib.sha256(open(os.path.join(ROOT, "ndr_b200", "csrc", "apply_march.cuh"), "rb").read()).hexdigest()[:16]
+
+
+def _lib_check(rc):
+    from ndr_b200 import _lib
+    _lib.check(rc)
+
+
 def our_arm(args):
     import torch
     import torch.distributed as dist
     from ndr_b200 import _lib
     from ndr_b200 import slab as S
     import ndr_b200.pyVoxelFEM as V
-    from ndr_b200.voxelfem import _dev_ptr
 
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
     if not torch.cuda.is_available():
@@ -155,134 +311,108 @@ def our_arm(args):
     W, K = args.warmup, args.steps
     hbm_peak, peak_src = measured_peaks()
     L = _lib.lib()
+    t_start = time.perf_counter()
 
-    # ---- workload: weak scaling, one 128x64x64 block of element layers per GPU, slabs along axis 0 ----
+    # ---- headline workload: weak scaling, one 128x64x64 block of element layers per GPU, slabs along axis 0 ----
     gE = [GRID[0] * world, GRID[1], GRID[2]]
-    bbmin, bbmax = np.zeros(3), np.array([DOMAIN[0] * world, DOMAIN[1], DOMAIN[2]])
-    if world == 1:
-        tps = V.TensorProductSimulator([1, 1, 1], [bbmin, bbmax], gE)
-        tps.readMaterial(MATERIAL)
-        tps.setElementDensities(np.random.default_rng(88).uniform(0, 1, tps.numElements()))
-        tps.applyDisplacementsAndLoadsFromFile(BC)
-        tps.E_0, tps.E_min, tps.gamma = 1.0, 1e-4, 3.0
-        mg = tps.multigridSolver(args.levels)
-        halo_bytes = 0
-        apply_halo = None
-    else:
-        comm = S.make_nccl_comm(dist, rank, world)
-        sl = S.SlabSolver(gE, bbmin, bbmax, args.levels, rank, world, comm, S.dist_host_sum(dist, torch.device("cuda", local)), MATERIAL)
-        tps, lay = sl.tps, sl.layout
-        tps.setElementDensities(layer_densities(lay.layer_lo, lay.layer_hi, lay.plane_elems))
-        sl.apply_bc_file(BC)
-        tps.E_0, tps.E_min, tps.gamma = 1.0, 1e-4, 3.0
-        mg = sl.multigrid()
-        halo_bytes = lay.plane_nodes * 24
-        apply_halo = lambda u, o: _lib.check(L.vfem_mg_apply_k_halo(mg._h, _dev_ptr(u, u.numel()), _dev_ptr(o, o.numel()), 1))
-    nn_l, ne_l = tps.numNodes(), tps.numElements()
-    nn_global = (gE[0] + 1) * (gE[1] + 1) * (gE[2] + 1)
-    set_bytes = algorithmic_bytes(nn_l, ne_l)
-    nsets = max(2, int(np.ceil(2.5 * L2_BYTES / (16 * 3 * nn_l))))  # ring of u/Ku pairs larger than L2
-    gen = torch.Generator(device="cuda"); gen.manual_seed(89 + rank)
-    us = [torch.randn(nn_l, 3, dtype=torch.float64, device="cuda", generator=gen) for _ in range(nsets)]
-    outs = [torch.empty(nn_l, 3, dtype=torch.float64, device="cuda") for _ in range(nsets)]
-
-    def sync_all():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def step(k):  # the local matrix-free apply; N > 1: + the halo shift of u (one node plane per interior face over NVLink),
-        # hidden behind the interior element layers
-        if apply_halo:
-            apply_halo(us[k % nsets], outs[k % nsets])
-        else:
-            tps.applyK(us[k % nsets], out=outs[k % nsets])
-
-    for k in range(W):
-        step(k)
-    sync_all()
+    wl = Workload(V, S, torch, dist, gE, [DOMAIN[0] * world, DOMAIN[1], DOMAIN[2]], BC, args.levels, rank, world, local, "flat")
     sampler = ClockSampler(local); sampler.start()
-    launches0 = L.vfem_launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sync_all()
-    ev0.record()
-    for k in range(K):
-        step(k)
-    ev1.record()
-    sync_all()
-    ms = ev0.elapsed_time(ev1)
-    launches = L.vfem_launch_count() - launches0
-    # keep the GPU busy long enough for nvidia-smi to see clocks under load (not part of the measurement)
-    t_end = time.perf_counter() + 0.6
-    while time.perf_counter() < t_end:
-        for k in range(50):
-            tps.applyK(us[k % nsets], out=outs[k % nsets])
-        torch.cuda.synchronize()
+    ms, kms, launches, nsets, bufs = time_kapply(L, torch, dist, wl, W, K, 89 + rank)
     clocks = sampler.stop()
-    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    value = 3.0 * nn_global * K / (ms * 1e-3) / 1e9
-
-    # ---- dominant kernel alone (no halo exchange): roofline ----
-    torch.cuda.synchronize()
-    ev0.record()
-    for k in range(K):
-        tps.applyK(us[k % nsets], out=outs[k % nsets])
-    ev1.record(); torch.cuda.synchronize()
-    kms = ev0.elapsed_time(ev1) / K
-    achieved = set_bytes / (kms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "applyMarchKernel<0,...> (matrix-free K(rho)u, element-marching Walsh-Hadamard form)", "achieved": achieved,
-                "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": set_bytes, "kernel_ms": kms, "gdof_per_s_per_gpu": 3.0 * nn_l / (kms * 1e-3) / 1e9}
-    tp = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tp):
-        roofline["traffic"] = json.load(open(tp)).get("apply_march_dram_bytes_per_launch")
+    value = 3.0 * wl.nn_global * K / (ms * 1e-3) / 1e9
+    roofline = roofline_block(wl, kms, hbm_peak, peak_src)
 
     # ---- MG-PCG solve over all ranks (collective: every rank takes part) ----
-    solve = None
+    solve = gpu_sol = None
     if not args.no_solve:
-        solve = time_solve(V, torch, args, tps, mg, world, dist)
+        solve, gpu_sol = time_solve(V, torch, wl, dist, keep_solution=(world == 1))
+
+    # ---- e2e: the reference-facing call with HOST buffers, H2D + D2H inside the timed region; every rank runs its slab's
+    # host-array apply at the same time (they share the host memory system and PCIe switches), time = max over ranks ----
+    e2e = time_e2e(torch, dist, wl, world, K)
+    del bufs
+    torch.cuda.empty_cache()
+
+    # ---- the other BASELINE configurations (strong scaling across the N ranks) ----
+    configs = {}
+    if not args.no_extra:
+        configs = extra_configs(args, V, S, torch, dist, L, rank, world, local, hbm_peak, peak_src)
 
     if rank != 0:
         if world > 1:
             dist.barrier(); dist.destroy_process_group()
         return
 
-    # ---- e2e: the reference-facing call with host buffers (pinned), H2D + D2H inside the timed region ----
-    uh = torch.randn(nn_l, 3, dtype=torch.float64).pin_memory().numpy()
-    oh = torch.empty(nn_l, 3, dtype=torch.float64).pin_memory().numpy()
-    ke = max(3, min(K, 20))
-    for _ in range(2):
-        tps.applyK(uh, out=oh)
-    torch.cuda.synchronize(); ev0.record()
-    for _ in range(ke):
-        tps.applyK(uh, out=oh)
-    ev1.record(); torch.cuda.synchronize()
-    e2e_ms = ev0.elapsed_time(ev1) / ke
-    e2e = {"value": 3.0 * nn_l * world / (e2e_ms * 1e-3) / 1e9, "unit": "GDOF/s", "h2d_bytes_per_step": int(uh.nbytes), "d2h_bytes_per_step": int(oh.nbytes),
-           "ms_per_step": e2e_ms, "call": "pyVoxelFEM TensorProductSimulator.applyK(numpy) -> vfem_tps_apply_k(VFEM_HOST), rank 0's slab"}
-
-    cpu = run_cpu_kapply(args.cpu_seconds, solve=not args.no_solve) if world == 1 and not args.no_cpu else None
+    cpu = parity = None
+    if world == 1 and not args.no_cpu:
+        cpu, cpu_sol = run_cpu_kapply(args.cpu_seconds, solve=not args.no_solve)
+        if cpu_sol is not None and gpu_sol is not None:
+            parity = parity_block(gpu_sol, cpu_sol)
     line = {"metric": "k_apply_gdof_per_s", "value": value, "unit": "GDOF/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "3D cantilever %dx%dx%d Q1 hex (128x64x64 element layers per GPU, slabs along axis 0), matrix-free K(rho)u, "
-                                   "seed-88 uniform(0,1) densities, E_min=1e-4, p=3" % tuple(gE),
-                       "dofs": 3 * nn_global, "l2": "ring of %d u/Ku buffer pairs (%.0f MB) > 126 MB L2" % (nsets, nsets * 48 * nn_l / 1e6),
-                       "halo": "none" if world == 1 else "1 node plane (%d B) per interior face per apply, ncclSend/ncclRecv on the solver stream" % halo_bytes},
+            "config": workload_config(gE, world, nsets, wl.nn_l),
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline}
+    line["config"]["timing"] = "the K applies are issued by one C-ABI call (vfem_tps_apply_k_ring / vfem_mg_apply_k_halo_ring) between two CUDA events"
     if solve:
         line["solve"] = solve
     if cpu:
         line["cpu_baseline"] = cpu
+    if parity:
+        line["parity"] = parity
+    if configs:
+        line["configs"] = configs
+    line["bench_wall_s"] = time.perf_counter() - t_start
     emit(line)
     if world > 1:
         dist.barrier(); dist.destroy_process_group()
 
 
-def time_solve(V, torch, args, g, mg, world, dist, reps=5):
-    """ms per MG-PCG solve of the bench grid (all ranks), reference production settings (fem.py:66-70)."""
+def parity_block(gpu_sol, cpu_sol):
+    """GPU MG-PCG solve vs the oracle's solve of the same system (both: zero start, tol 1e-4, FMG, 2 sweeps)"""
+    ug, uo, f = gpu_sol["u"], cpu_sol["u"], cpu_sol["f"]
+    cg, co = 0.5 * float(np.sum(f * ug)), 0.5 * float(np.sum(f * uo))
+    return {"against": "oracle restatement, same grid / loads / densities, same solver settings",
+            "u_rel_err_max": float(np.max(np.abs(ug - uo)) / np.max(np.abs(uo))), "compliance_rel_err": abs(cg - co) / abs(co),
+            "iterations_gpu": gpu_sol["iterations"], "iterations_oracle": cpu_sol["iterations"],
+            "residual_gpu": gpu_sol["residual"], "residual_oracle": cpu_sol["residual"], "compliance_gpu": cg, "compliance_oracle": co}
+
+
+def time_e2e(torch, dist, wl, world, K):
+    tps, nn_l = wl.tps, wl.nn_l
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ke = max(3, min(K, 20))
+    res = {}
+    for kind in ("pinned", "pageable"):
+        if kind == "pinned":
+            uh = torch.randn(nn_l, 3, dtype=torch.float64).pin_memory().numpy()
+            oh = torch.empty(nn_l, 3, dtype=torch.float64).pin_memory().numpy()
+        else:  # what fem.py's callers pass: plain numpy arrays
+            uh = np.random.default_rng(5).standard_normal((nn_l, 3)); oh = np.empty((nn_l, 3))
+        for _ in range(3):
+            tps.applyK(uh, out=oh)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter(); ev0.record()
+        for _ in range(ke):
+            tps.applyK(uh, out=oh)
+        ev1.record(); torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) / ke * 1e3
+        t = torch.tensor([max(ev0.elapsed_time(ev1) / ke, wall)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        res[kind] = float(t.item())
+    h2d = int(nn_l * 24)
+    return {"value": 3.0 * wl.nn_global / (res["pinned"] * 1e-3) / 1e9, "unit": "GDOF/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": h2d,
+            "ms_per_step": res["pinned"], "buffers": "pinned host arrays",
+            "pageable": {"value": 3.0 * wl.nn_global / (res["pageable"] * 1e-3) / 1e9, "ms_per_step": res["pageable"]},
+            "call": "pyVoxelFEM TensorProductSimulator.applyK(numpy) -> vfem_tps_apply_k(VFEM_HOST); all %d ranks run their slab's call "
+                    "concurrently, time = max over ranks (host clock around the loop, device synchronised)" % world}
+
+
+def time_solve(V, torch, wl, dist, reps=5, keep_solution=False, e2e=True):
+    """ms per MG-PCG solve (all ranks), reference production settings (fem.py:66-70)."""
+    g, mg, world = wl.tps, wl.mg, wl.world
     f = torch.from_numpy(g.buildLoadVector()).cuda()
     u0 = torch.zeros_like(f); out = torch.empty_like(f)
     kw = dict(mgIterations=1, mgSmoothingIterations=2, fullMultigrid=True, out=out)
@@ -300,22 +430,61 @@ def time_solve(V, torch, args, g, mg, world, dist, reps=5):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     its = mg.lastIterations
-    nn_global = (GRID[0] * world + 1) * (GRID[1] + 1) * (GRID[2] + 1)
-    res = {"ms_per_solve": ms, "iterations": int(its), "dofs": 3 * nn_global, "mdof_per_s": 3 * nn_global / ms / 1e3, "n_gpus": world,
-           "protocol": "zero initial guess, tol 1e-4, %d coarsening levels, FMG preconditioner, 2 GS sweeps, operator refresh included" % args.levels,
+    res = {"ms_per_solve": ms, "iterations": int(its), "dofs": 3 * wl.nn_global, "mdof_per_s": 3 * wl.nn_global / ms / 1e3, "n_gpus": world,
+           "ms_per_iteration": ms / max(1, int(its)),
+           "protocol": "zero initial guess, tol 1e-4, %d coarsening levels, FMG preconditioner, 2 GS sweeps, operator refresh included" % wl.levels,
            "residual": mg.lastResidualNorm}
-    if world == 1:
+    sol = None
+    if keep_solution:
+        sol = {"u": out.cpu().numpy(), "iterations": int(its), "residual": float(mg.lastResidualNorm)}
+    if world == 1 and e2e:
         # e2e: densities (host) in -> solve -> compliance + per-voxel gradient (host) out, as VoxelFEMFunction.forward does (fem.py:109-129)
         rho = g.getDensities()
         obj = V.MultigridComplianceObjective(mg)
         obj.tol, obj.zeroInit = 1e-4, True
-        obj.updateCache(rho); obj.compliance(); obj.gradient()
-        t0 = time.perf_counter()
-        for _ in range(3):
+        for _ in range(2):
+            obj.updateCache(rho); obj.compliance(); obj.gradient()
+        ts = []
+        for _ in range(5):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
             obj.updateCache(rho); J = obj.compliance(); gr = obj.gradient()
-        res["e2e_ms_densities_to_gradient"] = (time.perf_counter() - t0) / 3 * 1e3
+            ts.append((time.perf_counter() - t0) * 1e3)
+        res["e2e_ms_densities_to_gradient"] = float(np.median(ts))
+        res["e2e_ms_densities_to_gradient_min_max"] = [float(min(ts)), float(max(ts))]
         res["compliance"] = float(J)
-    return res
+    return res, sol
+
+
+def extra_configs(args, V, S, torch, dist, L, rank, world, local, hbm_peak, peak_src):
+    """BASELINE configs[2] and [3] in the same driver-run record: K-apply (+ halo) and one MG-PCG solve, STRONG scaling over the
+    `world` ranks.  256x128x128 uses the reference's own mgl = 3 (logs/slurm/gt/c1001.log); 512x256x256 needs 5 levels (its
+    mgl-3 coarsest grid, 64x32x32, is too large for the block-tridiagonal factor)."""
+    fix3 = os.path.join(FIX, "bcs", "3d")
+    cases = [("bridge_256x128x128", [256, 128, 128], [4.0, 2.0, 1.0], os.path.join(fix3, "bridge.bc"), 3),
+             ("cantilever_512x256x256", [512, 256, 256], [2.0, 1.0, 1.0], os.path.join(fix3, "cantilever_flexion.bc"), 5)]
+    out = {}
+    for name, gE, dom, bc, levels in cases:
+        if (gE[0] // world) % (1 << levels) or world > 8:
+            continue
+        if name.startswith("cantilever_512") and world not in (1, 8) and not args.all_extra:
+            continue
+        try:
+            wl = Workload(V, S, torch, dist, gE, dom, bc, levels, rank, world, local, "layers")
+            ms, kms, launches, nsets, bufs = time_kapply(L, torch, dist, wl, 3, 10, 189 + rank, preheat_s=0.1)
+            del bufs
+            solve, _ = time_solve(V, torch, wl, dist, reps=2, e2e=False)
+            ent = {"grid": gE, "dofs": 3 * wl.nn_global, "n_gpus": world, "scaling": "strong", "levels": levels,
+                   "k_apply_gdof_per_s": 3.0 * wl.nn_global * 10 / (ms * 1e-3) / 1e9, "k_apply_ms": ms / 10,
+                   "roofline": roofline_block(wl, kms, hbm_peak, peak_src), "solve": solve}
+            out[name] = ent
+            del wl
+            torch.cuda.empty_cache()
+        except Exception as e:  # noqa: BLE001  (a config that does not fit must not take the headline down)
+            out[name] = {"error": "%s: %s" % (type(e).__name__, e)}
+            if world > 1:
+                raise
+    return out
 
 
 _JSON_FD = None
@@ -345,6 +514,8 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-solve", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the 256x128x128 / 512x256x256 configurations")
+    ap.add_argument("--all-extra", action="store_true", help="512x256x256 at every N (default: N = 1 and 8)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

@@ -62,6 +62,9 @@ int vfem_tps_set_element_density(vfem_tps_t h, size_t ei, double v);            
 int vfem_tps_element_density(vfem_tps_t h, size_t ei, double *v);                   /* elementDensity */
 int vfem_tps_get_densities(vfem_tps_t h, double *rho, int memspace);                /* getDensities */
 int vfem_tps_apply_k(vfem_tps_t h, const double *u, double *out, int memspace);     /* applyK (TPS.hh:905-952) */
+/* `count` applyK calls issued back to back by one host call (no reference counterpart; a caller that applies K to many
+ * fields, and bench.py's timed loop): call k reads us[(start + k) % nsets] and writes outs[(start + k) % nsets]; device arrays */
+int vfem_tps_apply_k_ring(vfem_tps_t h, const double *const *us, double *const *outs, size_t nsets, size_t start, size_t count);
 /* kernel selection for the fine-level apply (no reference counterpart): variant 0 = auto (element-marching
  * Walsh-Hadamard kernel when K0 has the required symmetry), 1 = per-node gather kernel, 2 = marching kernel
  * with dense 3x3 blocks (the variant used when K0 lacks the isotropic zero pattern).  info[7] =
@@ -120,6 +123,7 @@ int vfem_mg_create_slab(vfem_tps_t tps_local, size_t num_coarsening_levels, vfem
 int vfem_mg_owned_planes(vfem_mg_t h, size_t l, size_t *first, size_t *last);       /* owned node planes (inclusive) of level l, local indices */
 int vfem_mg_exchange(vfem_mg_t h, size_t l, double *v_device, int memspace);        /* refresh the ghost planes of a level-l vector (collective) */
 int vfem_mg_apply_k_halo(vfem_mg_t h, double *u_device, double *out_device, int memspace); /* ghost planes of u refreshed + out = K u on the local grid (owned planes valid); the shift overlaps the interior layers (collective) */
+int vfem_mg_apply_k_halo_ring(vfem_mg_t h, double *const *us, double *const *outs, size_t nsets, size_t start, size_t count); /* `count` vfem_mg_apply_k_halo calls over a ring of device arrays, issued by one host call (collective) */
 int vfem_mg_dot(vfem_mg_t h, const double *a, const double *b, int memspace, double *result); /* dot product over the owned dofs of all ranks (collective) */
 
 /* ---- MultigridComplianceObjective --------------------------------------------------------------- */

@@ -157,6 +157,8 @@ int vfem_tps_element_density(vfem_tps_t h, size_t ei, double *v) { API_TRY WITH_
 int vfem_tps_get_densities(vfem_tps_t h, double *rho, int ms) { API_TRY WITH_SIM(h, s.getDensities(rho, MemSpace(ms));); API_CATCH }
 int vfem_tps_apply_k(vfem_tps_t h, const double *u, double *out, int ms) {
     API_TRY WITH_SIM(h, if (ms == VFEM_HOST) { s.applyKHost(u, out); } else { s.applyK(u, out); }); API_CATCH }
+int vfem_tps_apply_k_ring(vfem_tps_t h, const double *const *us, double *const *outs, size_t nsets, size_t start, size_t count) {
+    API_TRY WITH_SIM(h, for (size_t k = 0; k < count; ++k) s.applyK(us[(start + k) % nsets], outs[(start + k) % nsets]);); API_CATCH }
 int vfem_tps_set_apply_variant(vfem_tps_t h, int variant) { API_TRY WITH_SIM(h, s.applyVariant = variant;); API_CATCH }
 int vfem_tps_apply_info(vfem_tps_t h, int *info) {
     API_TRY WITH_SIM(h, info[0] = s.useMarch() ? 1 : 0; info[1] = s.khatStructure; info[2] = s.marchPlan.cfg; info[3] = s.marchPlan.XC;
