@@ -13,7 +13,7 @@ OBJ = os.path.join(HERE, "build")
 SO = os.path.join(HERE, "libvfem_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 SOURCES = ["sim.cu", "mg.cu", "topopt.cu", "capi.cu", "comm.cu"]
-FLAGS = (["-DVFEM_MARCH_NOBAR"] if os.environ.get("VFEM_NOBAR") else []) + ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
 

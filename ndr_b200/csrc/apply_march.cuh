@@ -266,9 +266,7 @@ applyMarchKernel(Grid<3> g, KhatParam kh, const Real *__restrict__ Ey, const Rea
 #pragma unroll
             for (int c = 0; c < 3; ++c) sYsp[buf][sIdx / (3 * ZT) + 1][c] = zh[0][c] - zh[1][c];
         }
-#ifndef VFEM_MARCH_NOBAR
         __syncthreads();
-#endif
         if (flags & MF_YRECV) {
 #pragma unroll
             for (int c = 0; c < 3; ++c) res[c] += sYb[c * ZT];

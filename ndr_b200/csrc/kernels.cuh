@@ -125,48 +125,6 @@ __device__ __forceinline__ void fineNodeRow(const Grid<N> &g, const K0Param<N> &
     fineNodeRowCompute<N, WITH_M>(g, K, Ey, idx, un, acc, M);
 }
 
-// 3-D neighbourhood gather with 16-byte loads: the three z-neighbours of one (dx,dy) row are 9 contiguous doubles, fetched
-// as 5 aligned double2 (the window starts at the even double index at or below the row start) instead of 9 scalar
-// loads - on the stride-2 colour lattice every warp load touches 12-13 lines whatever its width, so L1 wavefronts
-// fall with the instruction count.  Rows whose window would leave the array (or an unaligned u) take the scalar path.
-template <bool WITH_M>
-__device__ __forceinline__ void fineNodeRowVec(const Grid<3> &g, const K0Param<3> &K, const Real *__restrict__ Ey, const Real *u,
-                                               const int *idx, Real *acc, Real *M) {
-    Real un[27][3];
-    const int n = flattenNode<3>(g, idx);
-    const long long nd = (long long)g.nn * 3;
-    const bool aligned = (reinterpret_cast<size_t>(u) & 15) == 0;
-#pragma unroll
-    for (int r = 0; r < 9; ++r) {
-        const int dx = r / 3 - 1, dy = r % 3 - 1;
-        const int vx = idx[0] + dx, vy = idx[1] + dy;
-        const bool okr = vx >= 0 && vx < g.n[0] && vy >= 0 && vy < g.n[1];
-        const long long d0 = (long long)(n + dx * g.ninc[0] + dy * g.ninc[1] - 1) * 3;
-        const long long ds = d0 & ~1LL;
-        const int off = int(d0 & 1LL);
-        Real w[10];
-        if (aligned && ds >= 0 && ds + 10 <= nd) {
-            const double2 *p = reinterpret_cast<const double2 *>(u + ds);
-#pragma unroll
-            for (int i = 0; i < 5; ++i) { const double2 t = p[i]; w[2 * i] = t.x; w[2 * i + 1] = t.y; }
-        } else {
-#pragma unroll
-            for (int i = 0; i < 10; ++i) { const long long a = ds + i; w[i] = (a >= 0 && a < nd) ? u[a] : 0.0; }
-        }
-#pragma unroll
-        for (int dz = 0; dz < 3; ++dz) {
-            const int vz = idx[2] + dz - 1;
-            const bool ok = okr && vz >= 0 && vz < g.n[2];
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                const Real v = off ? w[dz * 3 + c + 1] : w[dz * 3 + c];
-                un[r * 3 + dz][c] = ok ? v : 0.0;
-            }
-        }
-    }
-    fineNodeRowCompute<3, WITH_M>(g, K, Ey, idx, un, acc, M);
-}
-
 // ---- coarse levels: assembled 3^N-point block stencil ---------------------------------------------
 // Node-major, row after row: S[((n*N + a)*3^N + k)*N + b] = K_l[(n,a), (n + delta(k), b)] (zero for out-of-grid
 // neighbours), so the 3^N * N * N coefficients of one node are contiguous and a warp reads them fully coalesced.
@@ -296,110 +254,6 @@ __global__ void __launch_bounds__(kBlock, MINB) gsFineKernel(Grid<N> g, K0Param<
     gsNodeUpdate<N>(tt, M, dmask[n], forward != 0, u, n);
 }
 
-
-// one thread per node as gsFineKernel, neighbourhood gathered with 16-byte loads (fineNodeRowVec)
-template <int MINB>
-__global__ void __launch_bounds__(kBlock, MINB) gsFineVecKernel(Grid<3> g, K0Param<3> K, const Real *__restrict__ Ey, Real *u,
-                                                                const Real *__restrict__ b, const uint8_t *__restrict__ dmask, int colour,
-                                                                int forward) {
-    const int t = blockIdx.x * kBlock + threadIdx.x;
-    int idx[3];
-    if (!colourNode<3>(g, t, colour, idx)) return;
-    const int n = flattenNode<3>(g, idx);
-    Real acc[3] = {0.0, 0.0, 0.0}, M[9];
-#pragma unroll
-    for (int i = 0; i < 9; ++i) M[i] = 0.0;
-    fineNodeRowVec<true>(g, K, Ey, u, idx, acc, M);
-    Real tt[3];
-#pragma unroll
-    for (int c = 0; c < 3; ++c) tt[c] = b[size_t(n) * 3 + c] - acc[c];
-    gsNodeUpdate<3>(tt, M, dmask[n], forward != 0, u, n);
-}
-
-// Split form of the 3-D fine-level colour phase: a CTA of 8 warps updates 32 colour nodes, warp S computes the
-// contribution of incident element slot S of every node (8 nodes x 3 loads, 72 DFMA with K0 entries as constant-bank
-// operands, since S is a compile-time constant of the warp's code path), the 8 partial rows and diagonal blocks are
-// summed through shared memory in slot order (fixed order => bit-reproducible) and warp 0 does the node update.
-// One thread per node (gsFineKernel) holds the whole 27-node neighbourhood in registers (150 registers, 17 %
-// occupancy, 3 dependent FMA chains): 8x the threads at a third of the registers hide the FP64 latency instead.
-template <int S>
-__device__ __forceinline__ void gsSplitSlot(const Grid<3> &g, const K0Param<3> &K, const Real *__restrict__ Ey, const Real *u,
-                                            const int *idx, Real *part /*[12]: row (3), M (9)*/) {
-    constexpr int KS = 24;
-    constexpr int s0 = (S >> 2) & 1, s1 = (S >> 1) & 1, s2 = S & 1;
-    constexpr int loc = ((1 - s0) << 2) | ((1 - s1) << 1) | (1 - s2);
-    const int e0 = idx[0] - 1 + s0, e1 = idx[1] - 1 + s1, e2 = idx[2] - 1 + s2;
-    const bool ok = e0 >= 0 && e0 < g.E[0] && e1 >= 0 && e1 < g.E[1] && e2 >= 0 && e2 < g.E[2];
-#pragma unroll
-    for (int i = 0; i < 12; ++i) part[i] = 0.0;
-    if (!ok) return;
-    const Real Ee = Ey[e0 * g.einc[0] + e1 * g.einc[1] + e2];
-    const Real *ue = u + size_t(e0 * g.ninc[0] + e1 * g.ninc[1] + e2) * 3;
-    Real ra[3] = {0.0, 0.0, 0.0}, rb[3] = {0.0, 0.0, 0.0}; // two half sums: 6 independent FMA chains
-#pragma unroll
-    for (int q = 0; q < 8; ++q) {
-        const Real *p = ue + size_t(((q >> 2) & 1) * g.ninc[0] + ((q >> 1) & 1) * g.ninc[1] + (q & 1)) * 3;
-        const Real v0 = p[0], v1 = p[1], v2 = p[2];
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            Real &r = (q < 4) ? ra[c] : rb[c];
-            r = fma(K.k[(loc * 3 + c) * KS + q * 3 + 0], v0, r);
-            r = fma(K.k[(loc * 3 + c) * KS + q * 3 + 1], v1, r);
-            r = fma(K.k[(loc * 3 + c) * KS + q * 3 + 2], v2, r);
-        }
-    }
-#pragma unroll
-    for (int c = 0; c < 3; ++c) part[c] = Ee * (ra[c] + rb[c]);
-#pragma unroll
-    for (int c = 0; c < 3; ++c)
-#pragma unroll
-        for (int c2 = 0; c2 < 3; ++c2) part[3 + c * 3 + c2] = Ee * K.k[(loc * 3 + c) * KS + loc * 3 + c2];
-}
-
-constexpr int kGsSplitNodes = 32;
-static __global__ void __launch_bounds__(256, 3) gsFineSplitKernel(Grid<3> g, K0Param<3> K, const Real *__restrict__ Ey, Real *u,
-                                                            const Real *__restrict__ b, const uint8_t *__restrict__ dmask, int colour,
-                                                            int forward) {
-    __shared__ Real sPart[8][12][kGsSplitNodes];
-    __shared__ Real sSum[12][kGsSplitNodes];
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    int idx[3];
-    const bool valid = colourNode<3>(g, blockIdx.x * kGsSplitNodes + lane, colour, idx);
-    Real part[12];
-#pragma unroll
-    for (int i = 0; i < 12; ++i) part[i] = 0.0;
-    if (valid) {
-        switch (w) { // warp-uniform
-        case 0: gsSplitSlot<0>(g, K, Ey, u, idx, part); break;
-        case 1: gsSplitSlot<1>(g, K, Ey, u, idx, part); break;
-        case 2: gsSplitSlot<2>(g, K, Ey, u, idx, part); break;
-        case 3: gsSplitSlot<3>(g, K, Ey, u, idx, part); break;
-        case 4: gsSplitSlot<4>(g, K, Ey, u, idx, part); break;
-        case 5: gsSplitSlot<5>(g, K, Ey, u, idx, part); break;
-        case 6: gsSplitSlot<6>(g, K, Ey, u, idx, part); break;
-        default: gsSplitSlot<7>(g, K, Ey, u, idx, part); break;
-        }
-    }
-#pragma unroll
-    for (int i = 0; i < 12; ++i) sPart[w][i][lane] = part[i];
-    __syncthreads();
-    for (int i = w; i < 12; i += 8) { // slot order 0..7, as the one-thread form sums them
-        Real s = sPart[0][i][lane];
-#pragma unroll
-        for (int k = 1; k < 8; ++k) s += sPart[k][i][lane];
-        sSum[i][lane] = s;
-    }
-    __syncthreads();
-    if (w == 0 && valid) {
-        const int n = flattenNode<3>(g, idx);
-        Real tt[3], M[9];
-#pragma unroll
-        for (int c = 0; c < 3; ++c) tt[c] = b[size_t(n) * 3 + c] - sSum[c][lane];
-#pragma unroll
-        for (int i = 0; i < 9; ++i) M[i] = sSum[3 + i][lane];
-        gsNodeUpdate<3>(tt, M, dmask[n], forward != 0, u, n);
-    }
-}
 
 // ---- warp-per-node kernels for the assembled levels: persistent warps striding over the nodes ----
 constexpr int kWarpBlock = 256; // 8 warps per block

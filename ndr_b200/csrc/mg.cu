@@ -2,6 +2,7 @@
 #include "mg.h"
 #include "kernels.cuh"
 #include "kernels_mg.cuh"
+#include "gs_tile.cuh"
 #include "coarse_solve.cuh"
 #include <cublas_v2.h>
 #include <cusolverDn.h>
@@ -436,15 +437,15 @@ template <int N> void MG<N>::applyK(size_t l, const Real *u, Real *out) { applyM
 template <int N> void MG<N>::computeResidual(size_t l, const Real *u, const Real *b, Real *r) { applyMode<1>(l, u, b, r); }
 template <int N> void MG<N>::applyKMasked(size_t l, const Real *u, Real *out) { applyMode<2>(l, u, nullptr, out); }
 
-// 3-D only (the 2-D fine level keeps the one-thread-per-node form); variant 8 = split kernel, 16 = 16-byte gather loads
-static int gsVariantGlobal = 4;
-static inline void launchGsFineSplit(const Grid<3> &g, const K0Param<3> &K, const Real *Ey, Real *u, const Real *b, const uint8_t *dmask,
-                                     int colour, int forward, int cnt, cudaStream_t stream) {
-    if (gsVariantGlobal >= 16) { gsFineVecKernel<2><<<unsigned((cnt + kBlock - 1) / kBlock), kBlock, 0, stream>>>(g, K, Ey, u, b, dmask, colour, forward); return; }
-    gsFineSplitKernel<<<unsigned((cnt + kGsSplitNodes - 1) / kGsSplitNodes), 256, 0, stream>>>(g, K, Ey, u, b, dmask, colour, forward);
+// 3-D fine level: shared-memory tile kernel (gs_tile.cuh); needs a 16-byte aligned u for its bulk copies
+static inline bool launchGsFineTile(const Grid<3> &g, const K0Param<3> &K, const Real *Ey, Real *u, const Real *b, const uint8_t *dmask,
+                                    int colour, int forward, cudaStream_t stream) {
+    if (reinterpret_cast<size_t>(u) & 15) return false;
+    const GsTilePlan p = planGsTile(g, colour);
+    gsFineTileKernel<3><<<p.grid, kGsTileThreads, kGsTileSmem, stream>>>(g, K, Ey, u, b, dmask, colour, forward, p.tz);
+    return true;
 }
-static inline void launchGsFineSplit(const Grid<2> &, const K0Param<2> &, const Real *, Real *, const Real *, const uint8_t *, int, int, int,
-                                     cudaStream_t) {}
+static inline bool launchGsFineTile(const Grid<2> &, const K0Param<2> &, const Real *, Real *, const Real *, const uint8_t *, int, int, cudaStream_t) { return false; }
 
 // Halo traffic of a coloured sweep (slab mode): the colours whose axis-0 parity is even (the first half of the forward
 // order, MG.hh:292-294) only read odd ghost planes and vice versa, and own0 is even / own1 odd on interior faces, so a
@@ -459,12 +460,9 @@ void MG<N>::smoothColoured(size_t l, Real *u, const Real *b, bool forward) {
         const int cnt = colourCount<N>(L.g, colour);
         if (cnt > 0) {
             const unsigned blocks = unsigned((cnt + kBlock - 1) / kBlock);
-            if (l == 0) {
-                if (N == 3 && gsVariant >= 8) gsVariantGlobal = gsVariant;
-                if (N == 3 && gsVariant >= 8) launchGsFineSplit(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0, cnt, stream);
-                else if (gsVariant == 4) gsFineKernel<N, 4><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
-                else if (gsVariant == 3) gsFineKernel<N, 3><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
-                else gsFineKernel<N, 2><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
+            if (l == 0) { // gsVariant 0: one thread per node gathering from global memory (the 2-D path and the fallback)
+                if (!(N == 3 && gsVariant != 0 && launchGsFineTile(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0, stream)))
+                    gsFineKernel<N, 4><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
             }
             else gsStencilWarpKernel<N><<<warpGridBlocks(cnt), kWarpBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), colour, forward ? 1 : 0, cnt);
             VFEM_CHECK_LAUNCH(); countLaunch();

@@ -55,10 +55,14 @@ struct MG : MGBase {
     // once into a CUDA graph on a private stream and replayed per PCG iteration.
     struct PrecondKey {
         const Real *f = nullptr; size_t steps = 0, nu = 0; bool fmg = false, sym = true; int P = 0, planes = 0;
-        bool operator==(const PrecondKey &o) const { return f == o.f && steps == o.steps && nu == o.nu && fmg == o.fmg && sym == o.sym && P == o.P && planes == o.planes; }
+        unsigned long long k0Version = 0; int applyVariant = 0, gsVariant = 0; // K0 / Khat and the kernel choice are baked into the captured launches
+        bool operator==(const PrecondKey &o) const {
+            return f == o.f && steps == o.steps && nu == o.nu && fmg == o.fmg && sym == o.sym && P == o.P && planes == o.planes &&
+                   k0Version == o.k0Version && applyVariant == o.applyVariant && gsVariant == o.gsVariant;
+        }
     };
     bool useGraphs = true, fusedSweeps = true;
-    int gsVariant = 4;              // fine-level GS: resident CTAs per SM the register budget is sized for (2..4, experiment knob)
+    int gsVariant = 1;              // fine-level GS, 3-D: 1 = shared-memory tile kernel (gs_tile.cuh), 0 = per-node gather from global memory
     cudaStream_t captureStream = nullptr;
     cudaGraphExec_t pgExec = nullptr;
     PrecondKey pgKey;

@@ -55,6 +55,7 @@ template <int N>
 void MG<N>::precondition(const Real *f, size_t steps, size_t nu, bool fmg) {
     if (!useGraphs) { solve(nullptr, f, steps, nu, true, true, nullptr, fmg, lv[0].x.p); return; }
     PrecondKey key; key.f = f; key.steps = steps; key.nu = nu; key.fmg = fmg; key.sym = symmetricGS; key.P = coarseP; key.planes = coarsePlanes;
+    key.k0Version = sim->k0Version; key.applyVariant = sim->applyVariant; key.gsVariant = gsVariant;
     if (!pgExec || !(key == pgKey)) {
         if (pgExec) { cudaGraphExecDestroy(pgExec); pgExec = nullptr; }
         if (!captureStream) VFEM_CUDA(cudaStreamCreateWithFlags(&captureStream, cudaStreamNonBlocking));

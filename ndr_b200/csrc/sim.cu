@@ -83,6 +83,7 @@ void Sim<N>::updateK0() {
     for (int i = 0; i < KS; ++i)
         for (int j = i + 1; j < KS; ++j) K0.k[j * KS + i] = K0.k[i * KS + j];
     if (N == 3) khatStructure = computeKhat(K0.k, Khat);
+    ++k0Version;
     touchStiffness();
 }
 

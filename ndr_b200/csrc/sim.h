@@ -46,6 +46,7 @@ struct Sim : SimBase {
     DevBuf<Real> d_rho, d_Ey;
     bool EyDirty = true;
     unsigned long long densityVersion = 1; // bumped whenever K(rho) changes
+    unsigned long long k0Version = 1;      // bumped whenever K0 / Khat change (they are baked into captured graphs as kernel parameters)
 
     // Slab of a larger grid: this simulator holds the element layers [layerLo, layerLo + g.E[0]) of a grid
     // with globalE0 layers along axis 0.  mn/mx/spacing/h describe the GLOBAL domain, so node positions (and with them

@@ -282,8 +282,56 @@ class TensorProductSimulator:
         from .voxelfem_mg import MultigridSolver
         return MultigridSolver(self, numCoarseningLevels)
 
+    # --- mesh export / density import (host-side I/O: TPS.hh:470-492, 531-565) ---
+    def _node_positions(self):
+        nper = [e + 1 for e in self._elems]
+        idx = np.indices(nper).reshape(self.N, -1).T
+        spacing = (self._bbmax - self._bbmin) / np.array(self._elems, float)   # TPS.hh:274-279 (size / (n - 1))
+        return self._bbmin + idx * spacing
+
+    def getMesh(self):
+        """(V, F): node positions (numNodes, 3) and element corner indices in Gmsh ordering (TPS.hh:531-565)."""
+        P = self._node_positions()
+        V = np.zeros((P.shape[0], 3))
+        V[:, :self.N] = P
+        nper = [e + 1 for e in self._elems]
+        eidx = np.indices(self._elems).reshape(self.N, -1)
+        npe = 2 ** self.N
+        F = np.empty((eidx.shape[1], npe), np.int32)
+        cols = []
+        for n in range(npe):
+            loc = [(n >> (self.N - 1 - d)) & 1 for d in range(self.N)]
+            cols.append(np.ravel_multi_index([eidx[d] + loc[d] for d in range(self.N)], nper))
+        k = 0
+        for pair in range(npe // 2):  # counterclockwise on quads / on both quad faces of a hex
+            a, b = cols[2 * pair], cols[2 * pair + 1]
+            F[:, k], F[:, k + 1] = (a, b) if pair % 2 == 0 else (b, a)
+            k += 2
+        return V, F
+
+    def readDensities(self, materialPath, fieldName="density"):
+        """Per-element scalar field of a .msh file -> element densities, elements matched by their centre (TPS.hh:470-509)."""
+        import os
+        if os.path.splitext(materialPath)[1] != ".msh":
+            raise RuntimeError("Material file extension" + os.path.splitext(materialPath)[1] + " is not supported")
+        from .shims import mesh as _mesh
+        fp = (_mesh.MSHFieldParser3 if self.N == 3 else _mesh.MSHFieldParser2)(materialPath)
+        dens = fp.scalarField(fieldName, _mesh.DomainType.PER_ELEMENT)
+        elems, verts = fp.elements(), fp._V
+        if len(elems) != self.numElements():
+            raise RuntimeError("The number of elements in the mesh : %d and the number of elements of the simulator : %d must be equal."
+                               % (len(elems), self.numElements()))
+        lo, hi = verts.min(axis=0), verts.max(axis=0)
+        centre = verts[elems].mean(axis=1)
+        rel = (centre - lo)[:, :self.N] / np.where(hi - lo > 0, hi - lo, 1.0)[:self.N]
+        E = np.array(self._elems)
+        cell = np.minimum(np.floor(rel * E).astype(np.int64), E - 1)
+        rho = self.getDensities()
+        rho[np.ravel_multi_index(cell.T, self._elems)] = dens
+        self.setElementDensities(rho)
+
     def solve(self, f):
         raise RuntimeError("TensorProductSimulator.solve (CHOLMOD direct solve of the full system) is not part of the "
                            "device hot path; use multigridSolver(L).preconditionedConjugateGradient")
 
-    solveWithImposedLoads = getK = constantStrainLoad = readDensities = getMesh = solve
+    solveWithImposedLoads = getK = constantStrainLoad = solve

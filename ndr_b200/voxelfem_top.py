@@ -48,13 +48,23 @@ class PythonFilter(_Filter):
     def __init__(self):
         self.apply_cb = None
         self.backprop_cb = None
+        self._error = None  # an exception raised inside the ctypes callback (ctypes would only print it)
 
         def _cb(ctx, backprop, pin, pvars, pout, n):
             as_np = lambda p: np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_double)), shape=(n,))
-            if backprop:
-                self.backprop_cb(as_np(pin), as_np(pvars), as_np(pout))
-            else:
-                self.apply_cb(as_np(pin), as_np(pout))
+            try:
+                if backprop:
+                    if self.backprop_cb is None:
+                        raise RuntimeError("Backprop callback must be configured")   # Filter.hh:96
+                    self.backprop_cb(as_np(pin), as_np(pvars), as_np(pout))
+                else:
+                    if self.apply_cb is None:
+                        raise RuntimeError("Apply callback must be configured")      # Filter.hh:89
+                    self.apply_cb(as_np(pin), as_np(pout))
+            except BaseException as e:  # noqa: BLE001
+                if self._error is None:
+                    self._error = e
+                as_np(pout)[:] = np.nan  # never hand stale memory on as a filter result
         self._c_cb = FILTER_CB(_cb)
 
 
@@ -122,10 +132,20 @@ class TopologyOptimizationProblem:
     def numVars(self):
         return lib().vfem_top_num_vars(self._h)
 
+    def _reraise(self):
+        """exceptions raised inside PythonFilter callbacks during the last C call (the reference throws through pybind)"""
+        for f in self._filters:
+            e = getattr(f, "_error", None)
+            if e is not None:
+                f._error = None
+                raise e
+
     def setVars(self, x, forceUpdate=False):
         a = _Arg(x, self.numVars())
         ch = C.c_int(0)
-        check(lib().vfem_top_set_vars(self._h, a.ptr, a.ms, int(forceUpdate), C.byref(ch)))
+        rc = lib().vfem_top_set_vars(self._h, a.ptr, a.ms, int(forceUpdate), C.byref(ch))
+        self._reraise()
+        check(rc)
         return bool(ch.value)
 
     def _get(self, which, out=None):
@@ -150,10 +170,12 @@ class TopologyOptimizationProblem:
     def evaluateObjectiveGradient(self, out=None):
         """numpy array by default; pass a float64 CUDA array as `out` to receive the gradient with no copy."""
         if out is not None and _is_device(out):
-            check(lib().vfem_top_objective_gradient(self._h, _dev_ptr(out, self.numVars()), DEVICE))
+            rc = lib().vfem_top_objective_gradient(self._h, _dev_ptr(out, self.numVars()), DEVICE)
+            self._reraise(); check(rc)
             return out
         g = np.empty(self.numVars())
-        check(lib().vfem_top_objective_gradient(self._h, _ptr(g), HOST))
+        rc = lib().vfem_top_objective_gradient(self._h, _ptr(g), HOST)
+        self._reraise(); check(rc)
         return g
 
     def evaluateConstraints(self):
@@ -163,7 +185,8 @@ class TopologyOptimizationProblem:
 
     def evaluateConstraintsJacobian(self):
         j = np.empty((len(self._constraints), self.numVars()))
-        check(lib().vfem_top_constraints_jacobian(self._h, _ptr(j), HOST))
+        rc = lib().vfem_top_constraints_jacobian(self._h, _ptr(j), HOST)
+        self._reraise(); check(rc)
         return j
 
 
@@ -177,7 +200,8 @@ class OCOptimizer:
 
     def step(self, m=0.2, ctol=1e-6):
         lam, nev = C.c_double(), C.c_int()
-        check(lib().vfem_oc_step(self._p._h, float(m), float(ctol), C.byref(lam), C.byref(nev)))
+        rc = lib().vfem_oc_step(self._p._h, float(m), float(ctol), C.byref(lam), C.byref(nev))
+        self._p._reraise(); check(rc)
         self.lastLambda, self.lastEvaluations = lam.value, nev.value
         # the reference prints "objective, constraint, lambda estimate" here (OptimalityCriterion.hh:74)
         print("objective, constraint, lambda estimate: %g\t%g\t%g" % (self._p.evaluateObjective(), self._p.evaluateConstraints()[0], lam.value))
