@@ -62,6 +62,7 @@ int vfem_tps_set_element_density(vfem_tps_t h, size_t ei, double v);            
 int vfem_tps_element_density(vfem_tps_t h, size_t ei, double *v);                   /* elementDensity */
 int vfem_tps_get_densities(vfem_tps_t h, double *rho, int memspace);                /* getDensities */
 int vfem_tps_apply_k(vfem_tps_t h, const double *u, double *out, int memspace);     /* applyK (TPS.hh:905-952) */
+int vfem_tps_solve(vfem_tps_t h, const double *f, double *u, int memspace);          /* solve(f) (TPS.hh:834-865): Dirichlet rows/cols removed, block LDL^T refreshed once per density update */
 /* `count` applyK calls issued back to back by one host call (no reference counterpart; a caller that applies K to many
  * fields, and bench.py's timed loop): call k reads us[(start + k) % nsets] and writes outs[(start + k) % nsets]; device arrays */
 int vfem_tps_apply_k_ring(vfem_tps_t h, const double *const *us, double *const *outs, size_t nsets, size_t start, size_t count);
@@ -128,6 +129,7 @@ int vfem_mg_dot(vfem_mg_t h, const double *a, const double *b, int memspace, dou
 
 /* ---- MultigridComplianceObjective --------------------------------------------------------------- */
 int vfem_obj_create(vfem_mg_t mg, vfem_obj_t *out);                                 /* ctor solves once (Objective.hh:78-82) */
+int vfem_obj_create_direct(vfem_tps_t tps, vfem_obj_t *out);                        /* pyVoxelFEM.ComplianceObjective(simulator) (VoxelFEM.cc:160-163, Objective.hh:25-68): direct solve per update */
 void vfem_obj_destroy(vfem_obj_t h);
 int vfem_obj_set_params(vfem_obj_t h, size_t cg_iter, double tol, size_t mg_iterations, size_t mg_smoothing_iterations, int full_multigrid, int zero_init);
 int vfem_obj_get_params(vfem_obj_t h, size_t *cg_iter, double *tol, size_t *mg_iterations, size_t *mg_smoothing_iterations, int *full_multigrid, int *zero_init);

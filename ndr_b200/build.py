@@ -43,7 +43,7 @@ def build(force=False, verbose=False):
     if verbose:
         for _, log in res:
             sys.stderr.write(log)
-    cmd = [NVCC, "-shared", "-o", SO] + [o for o, _ in res] + ["-lcusolver", "-lcublas", "-ldl", "-Xlinker", "-rpath=/usr/local/cuda/lib64"]
+    cmd = [NVCC, "-shared", "-o", SO] + [o for o, _ in res] + ["-ldl"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stderr)

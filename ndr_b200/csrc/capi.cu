@@ -139,7 +139,7 @@ int vfem_tps_set_dirichlet(vfem_tps_t h, const uint8_t *mask, const double *valu
             if (mask) { uint8_t m = 0; for (int c = 0; c < N; ++c) if (mask[n * N + c]) m |= uint8_t(1u << c); s.dmask[n] = m; }
             if (values) for (int c = 0; c < N; ++c) s.dval[n * N + c] = values[n * N + c];
         }
-        s.bcDirty = true;);
+        s.bcDirty = true; ++s.bcVersion;);
     API_CATCH }
 int vfem_tps_get_force_mask(vfem_tps_t h, uint8_t *mask) { API_TRY WITH_SIM(h, std::copy(s.hasForce.begin(), s.hasForce.end(), mask);); API_CATCH }
 int vfem_tps_build_load_vector(vfem_tps_t h, double *f, int ms) {
@@ -157,6 +157,9 @@ int vfem_tps_element_density(vfem_tps_t h, size_t ei, double *v) { API_TRY WITH_
 int vfem_tps_get_densities(vfem_tps_t h, double *rho, int ms) { API_TRY WITH_SIM(h, s.getDensities(rho, MemSpace(ms));); API_CATCH }
 int vfem_tps_apply_k(vfem_tps_t h, const double *u, double *out, int ms) {
     API_TRY WITH_SIM(h, if (ms == VFEM_HOST) { s.applyKHost(u, out); } else { s.applyK(u, out); }); API_CATCH }
+int vfem_tps_solve(vfem_tps_t h, const double *f, double *u, int ms) {
+    API_TRY WITH_SIM(h, Staged st(s.stream); const double *df = st.in(f, s.numDofs(), ms); double *du = st.out(u, s.numDofs(), ms);
+                     s.solveDirect(df, du); st.finish();); API_CATCH }
 int vfem_tps_apply_k_ring(vfem_tps_t h, const double *const *us, double *const *outs, size_t nsets, size_t start, size_t count) {
     API_TRY WITH_SIM(h, for (size_t k = 0; k < count; ++k) s.applyK(us[(start + k) % nsets], outs[(start + k) % nsets]);); API_CATCH }
 int vfem_tps_set_apply_variant(vfem_tps_t h, int variant) { API_TRY WITH_SIM(h, s.applyVariant = variant;); API_CATCH }

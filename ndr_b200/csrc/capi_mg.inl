@@ -168,6 +168,17 @@ int vfem_obj_create(vfem_mg_t mgh, vfem_obj_t *out) {
     *out = h;
     API_CATCH
 }
+int vfem_obj_create_direct(vfem_tps_t tps, vfem_obj_t *out) {
+    API_TRY
+    TpsH *t = (TpsH *)tps;
+    ObjH *h = new ObjH(); h->dim = t->dim;
+    try {
+        if (t->dim == 2) h->o2 = std::make_shared<Objective<2>>(t->s2);
+        else h->o3 = std::make_shared<Objective<3>>(t->s3);
+    } catch (...) { delete h; throw; }
+    *out = h;
+    API_CATCH
+}
 void vfem_obj_destroy(vfem_obj_t h) { delete (ObjH *)h; }
 int vfem_obj_set_params(vfem_obj_t h, size_t cg_iter, double tol, size_t mg_it, size_t nu, int fmg, int zero_init) {
     API_TRY WITH_OBJ(h, ob.cgIter = cg_iter; ob.tol = tol; ob.mgIterations = mg_it; ob.mgSmoothingIterations = nu; ob.fullMultigrid = fmg != 0; ob.zeroInit = zero_init != 0;); API_CATCH }

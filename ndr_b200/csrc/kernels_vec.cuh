@@ -69,6 +69,32 @@ static __global__ void __launch_bounds__(kRedBlock) dotKernel(const Real *__rest
     blockReduceAndFinish<1>(v, w.partials, w.ticket, out);
 }
 
+// y += alpha x
+static __global__ void __launch_bounds__(kRedBlock) axpyKernel(Real *__restrict__ y, const Real *__restrict__ x, Real alpha, size_t n) {
+    for (size_t i = size_t(blockIdx.x) * kRedBlock + threadIdx.x; i < n; i += size_t(gridDim.x) * kRedBlock) y[i] = fma(alpha, x[i], y[i]);
+}
+
+// reduction scratch of one owner (scalars on the device + a pinned host mirror)
+struct Reducer {
+    DevBuf<Real> partials, scal;
+    DevBuf<unsigned int> ticket;
+    Real *h = nullptr;
+    ReduceWork rw;
+    void init(cudaStream_t s) {
+        if (h) return;
+        partials.alloc(size_t(kRedMaxBlocks) * 4); scal.alloc(8); ticket.alloc(1);
+        scal.zero(s); ticket.zero(s);
+        rw.partials = partials.p; rw.ticket = ticket.p;
+        VFEM_CUDA(cudaMallocHost((void **)&h, 8 * sizeof(Real)));
+    }
+    Real fetch(int slot, cudaStream_t s) { // synchronous read-back of scal[slot]
+        VFEM_CUDA(cudaMemcpyAsync(h + slot, scal.p + slot, sizeof(Real), cudaMemcpyDeviceToHost, s));
+        VFEM_CUDA(cudaStreamSynchronize(s));
+        return h[slot];
+    }
+    ~Reducer() { if (h) cudaFreeHost(h); }
+};
+
 // out[0] = sum(a)
 static __global__ void __launch_bounds__(kRedBlock) sumKernel(const Real *__restrict__ a, size_t n, ReduceWork w, Real *out) {
     Real v[1] = {0.0};

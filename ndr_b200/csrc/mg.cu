@@ -3,20 +3,9 @@
 #include "kernels.cuh"
 #include "kernels_mg.cuh"
 #include "gs_tile.cuh"
-#include "coarse_solve.cuh"
-#include <cublas_v2.h>
-#include <cusolverDn.h>
+#include "block_tri.h"
 
 namespace vfem {
-
-static const size_t kMaxCoarseBytes = size_t(32) << 30; // block factors of the coarsest level
-
-#define VFEM_CUSOLVER(call)                                                                              \
-    do {                                                                                                 \
-        cusolverStatus_t s_ = (call);                                                                    \
-        if (s_ != CUSOLVER_STATUS_SUCCESS)                                                               \
-            throw std::runtime_error("cuSOLVER error " + std::to_string(int(s_)) + " at " + __FILE__ + ":" + std::to_string(__LINE__)); \
-    } while (0)
 
 template <int N>
 MG<N>::MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels, std::shared_ptr<SlabComm> comm_) : sim(fine), comm(comm_) {
@@ -84,7 +73,7 @@ MG<N>::MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels, std::shared_
     rw.partials = d_partials.p; rw.ticket = d_ticket.p;
     VFEM_CUDA(cudaMallocHost((void **)&h_scal, 8 * sizeof(Real)));
     d_C.alloc(size_t(NPE) * KS * KS);
-    d_info.alloc(1);
+    bt.reset(new BlockTri<N>());
     gCoarse = lv.back().g;
     if (slab()) {
         sim->computeLo = lv[0].g.own0 > 1 ? lv[0].g.own0 - 1 : 0;
@@ -143,16 +132,9 @@ MG<N>::~MG() {
     if (pgExec) cudaGraphExecDestroy(pgExec);
     if (captureStream) cudaStreamDestroy(captureStream);
     if (h_scal) cudaFreeHost(h_scal);
-    if (cusolverHandle) cusolverDnDestroy((cusolverDnHandle_t)cusolverHandle);
-    if (cublasHandle) cublasDestroy((cublasHandle_t)cublasHandle);
-    if (cusolverHandle2) cusolverDnDestroy((cusolverDnHandle_t)cusolverHandle2);
-    if (cublasHandle2) cublasDestroy((cublasHandle_t)cublasHandle2);
-    if (factorStream) cudaStreamDestroy(factorStream);
-    if (factorFork) cudaEventDestroy(factorFork);
     if (haloStream) cudaStreamDestroy(haloStream);
     if (haloFork) cudaEventDestroy(haloFork);
     if (haloJoin) cudaEventDestroy(haloJoin);
-    if (factorJoin) cudaEventDestroy(factorJoin);
 }
 
 template <int N>
@@ -222,98 +204,9 @@ void MG<N>::updateElementStiffnessMatrices(bool force) {
         comm->allreduceSum(Sg.p, Sg.n, stream);
         cS = Sg.p; cmask = dmaskG.p;
     }
-    const size_t nd = size_t(cgrid.nn) * N;
-    const int P = cgrid.ninc[0] * N, planes = cgrid.n[0];
-    const size_t PP = size_t(P) * P;
-    if (PP * size_t(6 * planes) * sizeof(Real) > kMaxCoarseBytes)
-        throw std::runtime_error("coarsest multigrid level has " + std::to_string(nd) + " dofs in planes of " + std::to_string(P) +
-                                 "; its block factorisation would need " + std::to_string(PP * size_t(6 * planes) * sizeof(Real) >> 20) +
-                                 " MB (use more coarsening levels)");
-    coarseDofs = int(nd); coarseP = P; coarsePlanes = planes;
-    const size_t offBlocks = size_t(planes > 1 ? planes - 1 : 1);
-    d_blkD.alloc(PP * planes); d_blkW.alloc(PP * planes); d_blkLo.alloc(PP * offBlocks);
-    d_Sinv.alloc(PP * planes); d_Trm.alloc(PP * offBlocks); d_Tcm.alloc(PP * offBlocks); d_z.alloc(nd);
-    d_blkD.zero(stream); d_blkLo.zero(stream);
-    {
-        long long tot = (long long)cgrid.nn * NST;
-        assembleBlockTriKernel<N><<<unsigned((tot + 127) / 128), 128, 0, stream>>>(cgrid, cS, cmask, d_blkD.p, d_blkLo.p, P);
-        VFEM_CHECK_LAUNCH(); countLaunch();
-        setIdentityBlocksKernel<<<296, 256, 0, stream>>>(d_blkW.p, P, planes);
-        VFEM_CHECK_LAUNCH(); countLaunch();
-    }
-    // two lanes: lane 0 (the solver's stream) eliminates the planes 0..mid-1 downwards, lane 1 (a private stream) the
-    // planes planes-1..mid+1 upwards; they meet at plane `mid` (ChainIdx in coarse_solve.cuh)
-    if (!cusolverHandle) {
-        for (int k = 0; k < 2; ++k) {
-            cusolverDnHandle_t hnd; VFEM_CUSOLVER(cusolverDnCreate(&hnd)); (k ? cusolverHandle2 : cusolverHandle) = hnd;
-            cublasHandle_t bh; if (cublasCreate(&bh) != CUBLAS_STATUS_SUCCESS) throw std::runtime_error("cublasCreate failed");
-            (k ? cublasHandle2 : cublasHandle) = bh;
-        }
-        VFEM_CUDA(cudaStreamCreateWithFlags(&factorStream, cudaStreamNonBlocking));
-        VFEM_CUDA(cudaEventCreateWithFlags(&factorFork, cudaEventDisableTiming));
-        VFEM_CUDA(cudaEventCreateWithFlags(&factorJoin, cudaEventDisableTiming));
-    }
-    struct Lane { cusolverDnHandle_t solver; cublasHandle_t blas; cudaStream_t s; Real *work; };
-    int lw = 0;
-    VFEM_CUSOLVER(cusolverDnDpotrf_bufferSize((cusolverDnHandle_t)cusolverHandle, CUBLAS_FILL_MODE_LOWER, P, d_blkD.p, P, &lw));
-    if (d_solverWork.n < size_t(2 * lw)) d_solverWork.alloc(size_t(2 * lw));
-    if (d_info.n < size_t(planes)) d_info.alloc(size_t(planes));
-    Lane lanes[2] = {{(cusolverDnHandle_t)cusolverHandle, (cublasHandle_t)cublasHandle, stream, d_solverWork.p},
-                     {(cusolverDnHandle_t)cusolverHandle2, (cublasHandle_t)cublasHandle2, factorStream, d_solverWork.p + lw}};
-    for (Lane &L : lanes) {
-        VFEM_CUSOLVER(cusolverDnSetStream(L.solver, L.s));
-        if (cublasSetStream(L.blas, L.s) != CUBLAS_STATUS_SUCCESS) throw std::runtime_error("cublasSetStream failed");
-    }
-    const Real one = 1.0, mone = -1.0, zero = 0.0;
-    auto gemm = [&](Lane &L, cublasOperation_t ta, cublasOperation_t tb, const Real *alpha, const Real *A, const Real *B, const Real *beta, Real *Cm) {
-        if (cublasDgemm(L.blas, ta, tb, P, P, P, alpha, A, P, B, P, beta, Cm, P) != CUBLAS_STATUS_SUCCESS) throw std::runtime_error("cublasDgemm failed");
-        countLaunch();
-    };
-    auto invert = [&](Lane &L, int p) { // S_p (in D_p) -> S_p^{-1}: Cholesky factor C_p, W_p = C_p^{-1} (solve C_p X = I), S_p^{-1} = W_p^T W_p
-        Real *Dp = d_blkD.p + PP * p, *Wp = d_blkW.p + PP * p, *Sp = d_Sinv.p + PP * p;
-        VFEM_CUSOLVER(cusolverDnDpotrf(L.solver, CUBLAS_FILL_MODE_LOWER, P, Dp, P, L.work, lw, d_info.p + p));
-        if (cublasDtrsm(L.blas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, P, P, &one, Dp, P, Wp, P) != CUBLAS_STATUS_SUCCESS)
-            throw std::runtime_error("cublasDtrsm failed");
-        countLaunch(2);
-        gemm(L, CUBLAS_OP_T, CUBLAS_OP_N, &one, Wp, Wp, &zero, Sp);
-    };
-    const int mid = planes / 2;
-    coarseMid = mid;
-    VFEM_CUDA(cudaEventRecord(factorFork, stream));
-    VFEM_CUDA(cudaStreamWaitEvent(factorStream, factorFork, 0));
-    for (int p = 0; p < mid; ++p) { // chain 0: block q = p holds T_{p+1} = A_{p+1,p} S_p^{-1}
-        Lane &L = lanes[0];
-        invert(L, p);
-        const Real *Ap = d_blkLo.p + PP * p, *Sp = d_Sinv.p + PP * p; // A_{p+1,p}
-        Real *Trm = d_Trm.p + PP * p, *Tcm = d_Tcm.p + PP * p, *Dn = d_blkD.p + PP * (p + 1);
-        gemm(L, CUBLAS_OP_N, CUBLAS_OP_N, &one, Ap, Sp, &zero, Tcm);  // T_{p+1}, column-major
-        gemm(L, CUBLAS_OP_N, CUBLAS_OP_T, &one, Sp, Ap, &zero, Trm);  // T_{p+1}^T column-major = T_{p+1} row-major
-        gemm(L, CUBLAS_OP_N, CUBLAS_OP_T, &mone, Tcm, Ap, &one, Dn);  // S_{p+1} = A_{p+1,p+1} - T_{p+1} A_{p+1,p}^T
-    }
-    for (int p = planes - 1; p > mid; --p) { // chain 1: block q = p-1 holds U_{p-1} = A_{p,p-1}^T S_p^{-1}
-        Lane &L = lanes[1];
-        invert(L, p);
-        const Real *Ap = d_blkLo.p + PP * (p - 1), *Sp = d_Sinv.p + PP * p; // A_{p,p-1}
-        Real *Trm = d_Trm.p + PP * (p - 1), *Tcm = d_Tcm.p + PP * (p - 1), *Dn = d_blkD.p + PP * (p - 1);
-        gemm(L, CUBLAS_OP_T, CUBLAS_OP_N, &one, Ap, Sp, &zero, Tcm);  // U_{p-1}, column-major
-        gemm(L, CUBLAS_OP_N, CUBLAS_OP_N, &one, Sp, Ap, &zero, Trm);  // U_{p-1}^T column-major = U_{p-1} row-major
-        if (p - 1 == mid) { // the middle plane also receives chain 0's update: serialise on the solver's stream
-            VFEM_CUDA(cudaEventRecord(factorJoin, factorStream));
-            VFEM_CUDA(cudaStreamWaitEvent(stream, factorJoin, 0));
-            gemm(lanes[0], CUBLAS_OP_N, CUBLAS_OP_N, &mone, Tcm, Ap, &one, Dn);
-        } else
-            gemm(L, CUBLAS_OP_N, CUBLAS_OP_N, &mone, Tcm, Ap, &one, Dn);  // S_{p-1} = A_{p-1,p-1} - U_{p-1} A_{p,p-1}
-    }
-    if (planes - 1 <= mid) { // no upward chain: nothing to join
-        VFEM_CUDA(cudaEventRecord(factorJoin, factorStream));
-        VFEM_CUDA(cudaStreamWaitEvent(stream, factorJoin, 0));
-    }
-    invert(lanes[0], mid);
-    std::vector<int> info(planes, 0);
-    VFEM_CUDA(cudaMemcpyAsync(info.data(), d_info.p, sizeof(int) * planes, cudaMemcpyDeviceToHost, stream));
-    VFEM_CUDA(cudaStreamSynchronize(stream));
-    for (int p = 0; p < planes; ++p)
-        if (info[p] != 0) throw std::runtime_error("Cholesky factorization failed: coarsest-level matrix not positive definite (plane " + std::to_string(p) + ", info " + std::to_string(info[p]) + ")");
+    bt->factor(cgrid, cS, cmask, stream);
+    coarseP = bt->P; coarsePlanes = bt->planes;
+    bt->check(stream);
     builtVersion = sim->densityVersion;
 }
 
@@ -330,47 +223,7 @@ void MG<N>::coarseSolve(const Real *b, Real *x) {
         comm->allreduceSum(bg.p, bg.n, stream);
         b = bg.p; x = xg.p; cmask = dmaskG.p;
     }
-    const bool pf = coarseP <= 256 && 2 * coarseP <= kChainSlots * kChainCluster * (kChainThreads / 32);
-    if (pf) { // small planes: one thread-block cluster, plane vector in distributed shared memory
-        const size_t smem = size_t(4) * coarseP * sizeof(Real);
-        ChainIdx ci{coarsePlanes, coarseMid};
-        cudaLaunchConfig_t cfg = {};
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-        cfg.blockDim = dim3(kChainThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
-        cfg.attrs = attr; cfg.numAttrs = 1;
-        if (chainCluster == 0) { // 16 CTAs (non-portable size) halve the matrix rows per SM and step; 8 where that does not fit
-            chainCluster = kChainCluster;
-            const char *v = getenv("VFEM_CHAIN_CLUSTER");
-            const int want = v ? atoi(v) : 16;
-            if (want > kChainCluster && want <= 16 &&
-                cudaFuncSetAttribute(blockTriChainKernel<N>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
-                cfg.gridDim = dim3(want); attr[0].val.clusterDim.x = want;
-                int n = 0;
-                if (cudaOccupancyMaxActiveClusters(&n, blockTriChainKernel<N>, &cfg) == cudaSuccess && n >= 1) chainCluster = want;
-            } else if (want >= 1 && want < kChainCluster && 2 * coarseP <= kChainSlots * want * (kChainThreads / 32)) chainCluster = want;
-            (void)cudaGetLastError();
-        }
-        cfg.gridDim = dim3(chainCluster); attr[0].val.clusterDim.x = chainCluster;
-        VFEM_CUDA(cudaLaunchKernelEx(&cfg, blockTriChainKernel<N>, coarseP, ci, (const Real *)d_Trm.p, (const Real *)d_Tcm.p,
-                                     (const Real *)d_Sinv.p, b, cmask, x, d_z.p));
-    } else { // large planes: the whole device, one grid barrier per chain step
-        if (chainGridBlocks == 0) {
-            int dev = 0, sms = 148;
-            VFEM_CUDA(cudaGetDevice(&dev));
-            VFEM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-            chainGridBlocks = sms;
-        }
-        int P = coarseP;
-        ChainIdx ci{coarsePlanes, coarseMid};
-        const Real *Trm = d_Trm.p, *Tcm = d_Tcm.p, *Sinv = d_Sinv.p; Real *zp = d_z.p;
-        void *args[] = {&P, &ci, &Trm, &Tcm, &Sinv, &b, &cmask, &x, &zp};
-        const size_t smem = size_t(2) * coarseP * sizeof(Real);
-        if (smem > 48 * 1024) VFEM_CUDA(cudaFuncSetAttribute(blockTriChainGridKernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-        VFEM_CUDA(cudaLaunchCooperativeKernel((const void *)blockTriChainGridKernel<N>, dim3(chainGridBlocks), dim3(kChainGridThreads), args, smem, stream));
-    }
-    countLaunch();
+    bt->solve(b, x, cmask, stream);
     if (slab()) // the local window (ghost planes included) of the global solution
         VFEM_CUDA(cudaMemcpyAsync(xl, xg.p + size_t(coarsePlaneOffset) * Lc.g.ninc[0] * N, size_t(Lc.g.nn) * N * sizeof(Real),
                                   cudaMemcpyDeviceToDevice, stream));

@@ -6,7 +6,7 @@
 // keeps a dense 24x24 Ke per coarse element (4.6 KB each) AND a block-CSC matrix per level; the
 // assembled stencil is the same linear operator, so smoothing/apply/restriction results agree to
 // roundoff.  The coarsest level is solved exactly through a block-tridiagonal LDL^T factorisation over
-// its node planes (cuSOLVER potrf + cuBLAS trsm/gemm per plane, refreshed once per density update) whose
+// its node planes (hand-written cooperative kernel, block_tri_factor.cuh, refreshed once per density update) whose
 // solves are one thread-block-cluster launch each (coarse_solve.cuh), where the reference calls CHOLMOD.
 #pragma once
 #include "sim.h"
@@ -15,6 +15,8 @@
 #include <functional>
 
 namespace vfem {
+
+template <int N> struct BlockTri;
 
 struct MGBase {
     int dim = 0;
@@ -35,17 +37,11 @@ struct MG : MGBase {
     std::shared_ptr<Sim<N>> sim;
     std::vector<Level> lv;
     DevBuf<Real> d_C;               // 2^N coarsened reference stiffness matrices (MG.hh:644-648)
-    // coarsest level: block-tridiagonal Cholesky over the node planes of axis 0 (coarse_solve.cuh)
-    DevBuf<Real> d_blkD, d_blkW, d_blkLo;   // S_p -> its Cholesky factor C_p, W_p = C_p^{-1}, A_{p+1,p}
-    DevBuf<Real> d_Sinv, d_Trm, d_Tcm, d_z; // S_p^{-1}, T_p (row- and column-major), chain scratch
-    int coarseP = 0, coarsePlanes = 0, coarseMid = 0;
-    void *cusolverHandle2 = nullptr, *cublasHandle2 = nullptr; // second lane of the two-ended factorisation
-    cudaStream_t factorStream = nullptr;
-    cudaEvent_t factorFork = nullptr, factorJoin = nullptr;
+    // coarsest level: block-tridiagonal LDL^T over the node planes of axis 0 (block_tri.h), refreshed once per density update
+    std::unique_ptr<BlockTri<N>> bt;
+    int coarseP = 0, coarsePlanes = 0;
     cudaStream_t haloStream = nullptr; // slab mode: the fine-level halo shift runs here, behind the interior K-apply
     cudaEvent_t haloFork = nullptr, haloJoin = nullptr;
-    int coarseDofs = 0;
-    void *cublasHandle = nullptr;
     unsigned long long builtVersion = 0;
     bool symmetricGS = true;                       // MG.hh:758
     bool buildBlockStiffnessMatrices = true;       // MG.hh:746 (kept for API parity; no effect on results)
@@ -75,8 +71,6 @@ struct MG : MGBase {
     DevBuf<Real> d_partials; DevBuf<unsigned int> d_ticket;
     Real *h_scal = nullptr;         // pinned mirror of d_scal
     ReduceWork rw;
-    void *cusolverHandle = nullptr;
-    DevBuf<Real> d_solverWork; DevBuf<int> d_info;
 
     // ---- slab decomposition -------------------------------------------------------------------------
     // Rank r owns the coarsest-level element layers [c0, c1) of axis 0 and, on every level l, the node planes
@@ -116,8 +110,7 @@ struct MG : MGBase {
     void applyKMasked(size_t l, const Real *u, Real *out);
     void smoothColoured(size_t l, Real *u, const Real *b, bool forward);               // MG.hh:336-340
     void smooth(size_t l, Real *u, const Real *b, bool forward, size_t sweeps);        // `sweeps` x smoothColoured, fused on the assembled levels
-    int sweepGridBlocks = 0, chainGridBlocks = 0;        // co-resident blocks of gsStencilSweepKernel (cooperative launch)
-    int chainCluster = 0;                                // CTAs of the cluster chain kernel (chosen at the first coarse solve)
+    int sweepGridBlocks = 0;                             // co-resident blocks of gsStencilSweepKernel (cooperative launch)
     void restriction(size_t lf, const Real *vf, Real *bc);                             // MG.hh:145-180
     void interpolate(size_t lf, const Real *xc, Real *xf, bool accumulate);            // MG.hh:115-141
     void zeroOutDirichlet(size_t l, Real *u);                                          // MG.hh:364-378

@@ -2,10 +2,89 @@
 #include "sim.h"
 #include "kernels.cuh"
 #include "kernels_vec.cuh"
+#include "block_tri.h"
 
 namespace vfem {
 
 unsigned long long g_launchCount = 0;
+
+// ---- direct solve (TPS::solve, TPS.hh:834-865) ----------------------------------------------------------------------
+// Fine-level operator assembled as a 3^N-point block stencil: S[n][k] = sum over the elements e containing both n and its
+// neighbour n + delta(k) of E_e K0[(loc_e(n), :), (loc_e(n + delta), :)]  (what TPS::m_assembleStiffnessMatrix, TPS.hh:589-625,
+// builds as a CSC matrix).  One thread per (node, slot).
+template <int N>
+static __global__ void __launch_bounds__(kBlock) buildFineStencilKernel(Grid<N> g, K0Param<N> K, const Real *__restrict__ Ey, Real *__restrict__ S) {
+    constexpr int NPE = 1 << N, KS = N * NPE, NST = ipow3(N);
+    const long long t = (long long)blockIdx.x * kBlock + threadIdx.x;
+    if (t >= (long long)g.nn * NST) return;
+    const int n = int(t / NST), k = int(t % NST);
+    int idx[N], dl[N];
+    unflattenNode<N>(g, n, idx);
+    { int tt = k; for (int d = N - 1; d >= 0; --d) { dl[d] = tt % 3 - 1; tt /= 3; } }
+    Real blk[N * N];
+#pragma unroll
+    for (int i = 0; i < N * N; ++i) blk[i] = 0.0;
+    for (int s = 0; s < NPE; ++s) {
+        int ei = 0, locI = 0, locJ = 0; bool ok = true;
+#pragma unroll
+        for (int d = 0; d < N; ++d) {
+            const int sd = (s >> (N - 1 - d)) & 1, e = idx[d] - 1 + sd;
+            ok = ok && e >= 0 && e < g.E[d];
+            const int li = 1 - sd, lj = li + dl[d];
+            ok = ok && lj >= 0 && lj <= 1;
+            ei += e * g.einc[d]; locI |= li << (N - 1 - d); locJ |= lj << (N - 1 - d);
+        }
+        if (!ok) continue;
+        const Real Ee = Ey[ei];
+#pragma unroll
+        for (int a = 0; a < N; ++a)
+#pragma unroll
+            for (int b = 0; b < N; ++b) blk[a * N + b] = fma(Ee, K.k[(locI * N + a) * KS + locJ * N + b], blk[a * N + b]);
+    }
+#pragma unroll
+    for (int i = 0; i < N * N; ++i) S[stencilIndex<N>(n, k, i)] = blk[i];
+}
+
+template <int N>
+struct DirectSolver {
+    DevBuf<Real> S, r, dx;
+    BlockTri<N> bt;
+    unsigned long long densityVersion = 0, k0Version = 0, bcVersion = 0;
+};
+
+template <int N>
+Sim<N>::~Sim() {
+    for (cudaStream_t st : {h2dStream, d2hStream, hostComputeStream}) if (st) cudaStreamDestroy(st);
+    for (int k = 0; k < kHostChunks; ++k) for (cudaEvent_t e : {evIn[k], evKernel[k], evOut[k]}) if (e) cudaEventDestroy(e);
+}
+
+template <int N>
+void Sim<N>::solveDirect(const Real *f, Real *u, int refinements) {
+    if (globalE0 != g.E[0]) throw std::runtime_error("direct solve is not available on a slab of a larger grid");
+    for (Real v : dval) if (v != 0.0) throw std::runtime_error("Non-zero Dirichlet conditions are not supported by the direct solver"); // TPS.hh:846-848 (the reference throws too)
+    syncBC();
+    if (!direct) direct.reset(new DirectSolver<N>());
+    DirectSolver<N> &ds = *direct;
+    const size_t nd = numDofs();
+    const Real *Ey = moduli();
+    if (ds.densityVersion != densityVersion || ds.k0Version != k0Version || ds.bcVersion != bcVersion) { // numeric factorisation (TPS.hh:854-858)
+        ds.S.alloc(size_t(g.nn) * NST * N * N); ds.r.alloc(nd); ds.dx.alloc(nd);
+        const long long tot = (long long)g.nn * NST;
+        buildFineStencilKernel<N><<<unsigned((tot + kBlock - 1) / kBlock), kBlock, 0, stream>>>(g, K0, Ey, ds.S.p);
+        VFEM_CHECK_LAUNCH(); countLaunch();
+        ds.bt.factor(g, ds.S.p, d_dmask.p, stream);
+        ds.bt.check(stream);
+        ds.densityVersion = densityVersion; ds.k0Version = k0Version; ds.bcVersion = bcVersion;
+    }
+    // the chain kernel masks its right-hand side and its result: the solution is 0 on the constrained dofs (TPS.hh:869-887)
+    ds.bt.solve(f, u, d_dmask.p, stream);
+    for (int it = 0; it < refinements; ++it) { // r = mask(f - K u) matrix-free, u += A^-1 r
+        applyFine<1>(u, f, d_dmask.p, ds.r.p);
+        ds.bt.solve(ds.r.p, ds.dx.p, d_dmask.p, stream);
+        axpyKernel<<<reduceBlocks(nd), kRedBlock, 0, stream>>>(u, ds.dx.p, 1.0, nd);
+        VFEM_CHECK_LAUNCH(); countLaunch();
+    }
+}
 
 template <int N>
 Sim<N>::Sim(const Real *bbmin, const Real *bbmax, const size_t *elems, size_t globalE0_, size_t layerLo_) {
@@ -121,7 +200,7 @@ void Sim<N>::setDirichlet(size_t ni, const uint8_t *compMask, const Real *value)
         if (!((dmask[ni] >> c) & 1)) { dmask[ni] |= uint8_t(1u << c); dval[ni * N + c] = value[c]; }
         else if (std::abs(dval[ni * N + c] - value[c]) > 1e-10) throw std::runtime_error("Conflicting dirichlet displacements.");
     }
-    bcDirty = true;
+    bcDirty = true; ++bcVersion;
 }
 
 template <int N>

@@ -11,6 +11,8 @@
 
 namespace vfem {
 
+template <int N> struct DirectSolver; // sim.cu: assembled fine operator + block-tridiagonal factor (TPS::solve)
+
 struct SimBase {
     int dim = 0;
     cudaStream_t stream = 0;
@@ -39,6 +41,7 @@ struct Sim : SimBase {
     std::vector<Real> force;           // nn*N
     std::vector<uint8_t> hasForce;     // nn
     bool bcDirty = true;
+    unsigned long long bcVersion = 1;  // bumped whenever the Dirichlet mask changes (the direct factorisation depends on it)
     DevBuf<uint8_t> d_dmask;
     DevBuf<Real> d_dval;
 
@@ -63,10 +66,7 @@ struct Sim : SimBase {
 
     // elems: local element counts; globalE0 = 0 means "not a slab" (the local grid is the whole grid)
     Sim(const Real *bbmin, const Real *bbmax, const size_t *elems, size_t globalE0 = 0, size_t layerLo = 0);
-    ~Sim() override {
-        for (cudaStream_t st : {h2dStream, d2hStream, hostComputeStream}) if (st) cudaStreamDestroy(st);
-        for (int k = 0; k < kHostChunks; ++k) for (cudaEvent_t e : {evIn[k], evKernel[k], evOut[k]}) if (e) cudaEventDestroy(e);
-    }
+    ~Sim() override;
 
     // TPS.hh:274-279
     void nodePosition(size_t ni, Real *p) const {
@@ -109,6 +109,11 @@ struct Sim : SimBase {
                                                int edgeSkip = 0); // edgeSkip bit 0 / 1: do not store the view's first / last node plane
     void applyKHost(const Real *hu, Real *hout);  // host arrays in / out, copies pipelined with the kernel
     void complianceGradient(const Real *u, Real *g); // TPS.hh:730-751
+    // u = K(rho)^{-1} f with the Dirichlet rows / columns removed (TPS::solve, TPS.hh:834-865); device pointers.
+    // The numeric factorisation is redone only when the densities, the material or the Dirichlet mask changed
+    // (m_numericFactorizationUpToDate).  refinements: steps of iterative refinement with the matrix-free residual.
+    void solveDirect(const Real *f, Real *u, int refinements = 2);
+    std::unique_ptr<DirectSolver<N>> direct;
 };
 
 } // namespace vfem

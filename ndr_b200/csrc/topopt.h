@@ -23,14 +23,16 @@ struct ProblemBase { int dim = 0; virtual ~ProblemBase() {} };
 template <int N>
 struct Objective : ObjectiveBase {
     std::shared_ptr<Sim<N>> sim;
-    std::shared_ptr<MG<N>> mg;
+    std::shared_ptr<MG<N>> mg;               // null: ComplianceObjective, the direct solve (Objective.hh:25-68)
     DevBuf<Real> u, f;
+    Reducer red;                             // reductions of the density pipeline (slots 5..7)
     size_t cgIter = 100; Real tol = 1e-5; size_t mgIterations = 1, mgSmoothingIterations = 2; // Objective.hh:96-99
     bool fullMultigrid = true, zeroInit = false;
     void (*residual_cb)(void *, size_t, Real) = nullptr; void *residual_ctx = nullptr;
     size_t lastIterations = 0; Real lastResidual = 0;
 
-    explicit Objective(std::shared_ptr<MG<N>> mg_);
+    explicit Objective(std::shared_ptr<MG<N>> mg_);    // MultigridComplianceObjective (Objective.hh:70-102)
+    explicit Objective(std::shared_ptr<Sim<N>> sim_);  // ComplianceObjective(simulator): every updateCache is a direct solve
     void updateCache(const Real *xPhysDev);  // Objective.hh:85-93
     Real compliance();                       // Objective.hh:39-41
     void gradient(Real *gDev) { sim->complianceGradient(u.p, gDev); } // Objective.hh:43-45

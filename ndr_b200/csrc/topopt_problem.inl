@@ -8,13 +8,27 @@ Objective<N>::Objective(std::shared_ptr<MG<N>> mg_) : sim(mg_->sim), mg(mg_) {
     sim->buildLoadVectorHost(fh.data());
     f.upload(fh, sim->stream);
     u.alloc(nd); u.zero(sim->stream);          // Objective.hh:80
+    red.init(sim->stream);
     updateCache(sim->d_rho.p);                  // Objective.hh:81: a full solve with the default knobs
+}
+
+template <int N>
+Objective<N>::Objective(std::shared_ptr<Sim<N>> sim_) : sim(sim_) {
+    dim = N;
+    const size_t nd = sim->numDofs();
+    std::vector<Real> fh(nd);
+    sim->buildLoadVectorHost(fh.data());       // Objective.hh:32
+    f.upload(fh, sim->stream);
+    u.alloc(nd); u.zero(sim->stream);
+    red.init(sim->stream);
+    updateCache(sim->d_rho.p);                  // Objective.hh:33
 }
 
 template <int N>
 void Objective<N>::updateCache(const Real *xPhysDev) {
     if (xPhysDev != sim->d_rho.p) sim->setDensities(xPhysDev, MS_DEVICE);
     else sim->touchStiffness();
+    if (!mg) { sim->solveDirect(f.p, u.p); lastIterations = 0; lastResidual = 0; return; } // Objective.hh:48-51
     if (zeroInit) u.zero(sim->stream);
     typename MG<N>::PcgCb cb;
     if (residual_cb) cb = [this](size_t it, const Real *, const Real *, Real rnorm) { residual_cb(residual_ctx, it, rnorm); };
@@ -22,7 +36,13 @@ void Objective<N>::updateCache(const Real *xPhysDev) {
 }
 
 template <int N>
-Real Objective<N>::compliance() { return 0.5 * mg->dot(f.p, u.p, sim->numDofs()); }
+Real Objective<N>::compliance() {
+    if (mg) return 0.5 * mg->dot(f.p, u.p, sim->numDofs());
+    const size_t n = sim->numDofs();
+    dotKernel<<<reduceBlocks(n), kRedBlock, 0, sim->stream>>>(f.p, u.p, n, red.rw, red.scal.p + 5);
+    VFEM_CHECK_LAUNCH(); countLaunch();
+    return 0.5 * red.fetch(5, sim->stream);
+}
 
 template <int N>
 Problem<N>::Problem(std::shared_ptr<Sim<N>> s, std::shared_ptr<Objective<N>> o, const std::vector<Real> &volFracs,
@@ -47,18 +67,16 @@ void Problem<N>::backpropFilter(const FilterDesc &f, const Real *in, const Real 
 template <int N>
 bool Problem<N>::setVars(const Real *x, MemSpace ms, bool forceUpdate) {
     const size_t ne = numVars();
-    MG<N> &mg = *obj->mg;
+    Reducer &red = obj->red;
     const Real *xd = x;
     if (ms == MS_HOST) { // stage the incoming design variables
         VFEM_CUDA(cudaMemcpyAsync(s0.p, x, ne * sizeof(Real), cudaMemcpyHostToDevice, sim->stream));
         xd = s0.p;
     }
     if (!forceUpdate && varsAreSet) { // Problem.hh:50-51
-        diffSqKernel<<<reduceBlocks(ne), kRedBlock, 0, sim->stream>>>(xd, cached[0].p, ne, mg.rw, mg.d_scal.p + 6);
+        diffSqKernel<<<reduceBlocks(ne), kRedBlock, 0, sim->stream>>>(xd, cached[0].p, ne, red.rw, red.scal.p + 6);
         VFEM_CHECK_LAUNCH(); countLaunch();
-        VFEM_CUDA(cudaMemcpyAsync(mg.h_scal + 6, mg.d_scal.p + 6, sizeof(Real), cudaMemcpyDeviceToHost, sim->stream));
-        VFEM_CUDA(cudaStreamSynchronize(sim->stream));
-        if (std::sqrt(mg.h_scal[6]) < 1e-16) return false;
+        if (std::sqrt(red.fetch(6, sim->stream)) < 1e-16) return false;
     }
     if (xd != cached[0].p) VFEM_CUDA(cudaMemcpyAsync(cached[0].p, xd, ne * sizeof(Real), cudaMemcpyDeviceToDevice, sim->stream));
     for (size_t i = 0; i < filters.size(); ++i) applyFilter(filters[i], cached[i].p, cached[i + 1].p);
@@ -87,13 +105,11 @@ void Problem<N>::evaluateObjectiveGradient(Real *gradDev) {
 
 template <int N>
 Real Problem<N>::meanOf(const Real *v) {
-    MG<N> &mg = *obj->mg;
+    Reducer &red = obj->red;
     const size_t ne = numVars();
-    sumKernel<<<reduceBlocks(ne), kRedBlock, 0, sim->stream>>>(v, ne, mg.rw, mg.d_scal.p + 7);
+    sumKernel<<<reduceBlocks(ne), kRedBlock, 0, sim->stream>>>(v, ne, red.rw, red.scal.p + 7);
     VFEM_CHECK_LAUNCH(); countLaunch();
-    VFEM_CUDA(cudaMemcpyAsync(mg.h_scal + 7, mg.d_scal.p + 7, sizeof(Real), cudaMemcpyDeviceToHost, sim->stream));
-    VFEM_CUDA(cudaStreamSynchronize(sim->stream));
-    return mg.h_scal[7] / Real(ne);
+    return red.fetch(7, sim->stream) / Real(ne);
 }
 
 template <int N>

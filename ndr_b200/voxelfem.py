@@ -330,8 +330,56 @@ class TensorProductSimulator:
         rho[np.ravel_multi_index(cell.T, self._elems)] = dens
         self.setElementDensities(rho)
 
-    def solve(self, f):
-        raise RuntimeError("TensorProductSimulator.solve (CHOLMOD direct solve of the full system) is not part of the "
-                           "device hot path; use multigridSolver(L).preconditionedConjugateGradient")
+    def solve(self, f, out=None):
+        """TPS::solve (TPS.hh:834-865): K(rho) u = f with the Dirichlet rows / columns removed; the factorisation is redone only
+        when the densities, the material or the Dirichlet mask changed.  Non-zero Dirichlet values throw, as in the reference."""
+        a = _Arg(f, self.numDoFs())
+        if a.ms == DEVICE:
+            if out is None:
+                raise RuntimeError("device-resident solve needs a preallocated `out` device array")
+            check(lib().vfem_tps_solve(self._h, a.ptr, _dev_ptr(out, self.numDoFs()), DEVICE))
+            return out
+        u = np.empty((self.numNodes(), self.N))
+        check(lib().vfem_tps_solve(self._h, a.ptr, _ptr(u), HOST))
+        return u
 
-    solveWithImposedLoads = getK = constantStrainLoad = solve
+    def solveWithImposedLoads(self):
+        return self.solve(self.buildLoadVector())   # TPS.hh:838-840
+
+    def constantStrainLoad(self, eps):
+        """Global load under the constant unit strain `eps` (TPS.hh:792-820 with Element::constantStrainLoad :167-173):
+        per element rho_e * vol * int eps(phi_j e_i) : C : eps = rho_e * (K0 u_eps)|_e for the affine field u_eps(x) = eps x
+        (scaled by the DENSITY, not the SIMP modulus, as in the reference).  Host-side helper of the homogenisation scripts."""
+        eps = _np(eps).reshape(self.N, self.N)
+        _, F = self._element_nodes()
+        ue = (self._node_positions() @ eps.T)[F].reshape(F.shape[0], -1)
+        le = (ue @ self.fullDensityElementStiffnessMatrix().T) * self.getDensities()[:, None]
+        out = np.zeros((self.numNodes(), self.N))
+        np.add.at(out, F.ravel(), le.reshape(-1, self.N))
+        return out
+
+    def getK(self):
+        """Assembled stiffness matrix (TPS.hh:966-973 -> m_assembleStiffnessMatrix :589-625), Dirichlet rows/columns included, as a
+        scipy.sparse CSC matrix (the reference returns MeshFEM's SuiteSparseMatrix; host-side export, not on the solve path)."""
+        import scipy.sparse as sp
+        K0 = self.fullDensityElementStiffnessMatrix()
+        rho = self.getDensities()
+        E0, Emin, g = self._simp()
+        Ee = Emin + rho ** g * (E0 - Emin)
+        _, F = self._element_nodes()
+        dofs = (F[:, :, None] * self.N + np.arange(self.N)[None, None, :]).reshape(F.shape[0], -1)
+        ks = dofs.shape[1]
+        rows = np.repeat(dofs, ks, axis=1).ravel()
+        cols = np.tile(dofs, (1, ks)).ravel()
+        vals = (Ee[:, None] * K0.ravel()[None, :]).ravel()
+        n = self.numDoFs()
+        return sp.csc_matrix((vals, (rows, cols)), shape=(n, n))
+
+    def _element_nodes(self):
+        nper = [e + 1 for e in self._elems]
+        eidx = np.indices(self._elems).reshape(self.N, -1)
+        cols = []
+        for n in range(2 ** self.N):
+            loc = [(n >> (self.N - 1 - d)) & 1 for d in range(self.N)]
+            cols.append(np.ravel_multi_index([eidx[d] + loc[d] for d in range(self.N)], nper))
+        return eidx, np.stack(cols, axis=1)

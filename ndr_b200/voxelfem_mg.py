@@ -227,8 +227,11 @@ class MultigridComplianceObjective:
         check(lib().vfem_obj_compliance(self._h, C.byref(J)))
         return J.value
 
+    def _sim(self):
+        return self.mg._tps if self.mg is not None else self._tps
+
     def gradient(self, out=None):
-        ne = self.mg._tps.numElements()
+        ne = self._sim().numElements()
         if out is not None and _is_device(out):
             check(lib().vfem_obj_gradient(self._h, _dev_ptr(out, ne), DEVICE))
             return out
@@ -237,17 +240,17 @@ class MultigridComplianceObjective:
         return g
 
     def u(self):
-        u = np.empty((self.mg._tps.numNodes(), self.mg.N))
+        u = np.empty((self._sim().numNodes(), self._sim().N))
         check(lib().vfem_obj_get_u(self._h, _ptr(u), HOST))
         return u
 
     def f(self):
-        f = np.empty((self.mg._tps.numNodes(), self.mg.N))
+        f = np.empty((self._sim().numNodes(), self._sim().N))
         check(lib().vfem_obj_get_f(self._h, _ptr(f), HOST))
         return f
 
     def updateCache(self, xPhys):
-        a = _Arg(xPhys, self.mg._tps.numElements())
+        a = _Arg(xPhys, self._sim().numElements())
         check(lib().vfem_obj_update_cache(self._h, a.ptr, a.ms))
 
     def lastSolve(self):
@@ -256,6 +259,15 @@ class MultigridComplianceObjective:
         return its.value, rn.value
 
 
-def ComplianceObjective(simulator):
-    raise RuntimeError("ComplianceObjective (CHOLMOD direct solve) is not part of the device hot path; "
-                       "use MultigridComplianceObjective(tps.multigridSolver(L))")
+class ComplianceObjective(MultigridComplianceObjective):
+    """pyVoxelFEM.ComplianceObjective(simulator) (VoxelFEM.cc:160-163, Objective.hh:25-68): every updateCache is a direct
+    solve (block LDL^T on the device where the reference calls CHOLMOD) - the `--mgl 0` path of fem.py:44-45."""
+    _FIELDS = ()
+
+    def __init__(self, simulator):
+        object.__setattr__(self, "mg", None)
+        object.__setattr__(self, "_tps", simulator)
+        object.__setattr__(self, "_h", C.c_void_p())
+        object.__setattr__(self, "_rcb", None)
+        object.__setattr__(self, "_rcb_c", None)
+        check(lib().vfem_obj_create_direct(simulator._h, C.byref(self._h)))
