@@ -89,6 +89,7 @@ int vfem_mg_apply_k(vfem_mg_t h, size_t l, const double *u, double *out, int mem
 int vfem_mg_compute_residual(vfem_mg_t h, size_t l, const double *u, const double *b, double *out, int memspace); /* computeResidual */
 int vfem_mg_zero_dirichlet(vfem_mg_t h, size_t l, double *u, int memspace);                          /* zeroOutDirichletComponents */
 int vfem_mg_smooth_colored(vfem_mg_t h, size_t l, double *u, const double *b, int forward, int memspace); /* smoothingMulticoloredGS (MG.hh:336-340) */
+int vfem_mg_smooth_serial(vfem_mg_t h, size_t l, double *u, const double *b, int forward, int memspace);  /* smoothing(l,u,b): serial lexicographic GS (MG.hh:269-282, VoxelFEM.cc:99-104; debug helper, one warp) */
 int vfem_mg_restrict(vfem_mg_t h, size_t l_fine, const double *v_fine, double *out_coarse, int memspace);   /* restriction (MG.hh:145-180) */
 int vfem_mg_interpolate(vfem_mg_t h, size_t l_fine, const double *x_coarse, double *x_fine, int accumulate, int memspace); /* MG.hh:115-141 */
 int vfem_mg_level_stencil(vfem_mg_t h, size_t l, double *out);                      /* debug: assembled operator of level l >= 1, (3^N, N, N, nn) */

@@ -70,6 +70,10 @@ int vfem_mg_compute_residual(vfem_mg_t h, size_t l, const double *u, const doubl
 int vfem_mg_zero_dirichlet(vfem_mg_t h, size_t l, double *u, int ms) {
     API_TRY WITH_MG(h, mg.syncMasks(); size_t n = mg.levelDofs(l); Staged st(mg.stream); double *du = st.out(u, n, ms, true);
                     mg.zeroOutDirichlet(l, du); st.finish();); API_CATCH }
+int vfem_mg_smooth_serial(vfem_mg_t h, size_t l, double *u, const double *b, int forward, int ms) {
+    API_TRY WITH_MG(h, MG_READY(l); size_t n = mg.levelDofs(l); Staged st(mg.stream);
+                    double *du = st.out(u, n, ms, true); const double *db = st.in(b, n, ms);
+                    mg.smoothSerial(l, du, db, forward != 0); st.finish();); API_CATCH }
 int vfem_mg_smooth_colored(vfem_mg_t h, size_t l, double *u, const double *b, int forward, int ms) {
     API_TRY WITH_MG(h, MG_READY(l); size_t n = mg.levelDofs(l); Staged st(mg.stream);
                     double *du = st.out(u, n, ms, true); const double *db = st.in(b, n, ms);

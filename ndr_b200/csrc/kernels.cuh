@@ -104,9 +104,9 @@ __device__ __forceinline__ void fineNodeRowCompute(const Grid<N> &g, const K0Par
     }
 }
 
-template <int N, bool WITH_M>
+template <int N, bool WITH_M, bool LDCG = false>
 __device__ __forceinline__ void fineNodeRow(const Grid<N> &g, const K0Param<N> &K, const Real *__restrict__ Ey,
-                                            const Real *__restrict__ u, const int *idx, Real *acc, Real *M) {
+                                            const Real *u, const int *idx, Real *acc, Real *M) {
     constexpr int NST = ipow3(N);
     Real un[NST][N];
 #pragma unroll
@@ -120,7 +120,7 @@ __device__ __forceinline__ void fineNodeRow(const Grid<N> &g, const K0Param<N> &
         }
         int base = flattenNode<N>(g, idx) + off;
 #pragma unroll
-        for (int c = 0; c < N; ++c) un[k][c] = ok ? u[size_t(base) * N + c] : 0.0;
+        for (int c = 0; c < N; ++c) un[k][c] = ok ? (LDCG ? __ldcg(u + size_t(base) * N + c) : u[size_t(base) * N + c]) : 0.0;
     }
     fineNodeRowCompute<N, WITH_M>(g, K, Ey, idx, un, acc, M);
 }
@@ -254,6 +254,40 @@ __global__ void __launch_bounds__(kBlock, MINB) gsFineKernel(Grid<N> g, K0Param<
     gsNodeUpdate<N>(tt, M, dmask[n], forward != 0, u, n);
 }
 
+
+// ---- serial lexicographic Gauss-Seidel (MG::smoothing, MG.hh:269-282; the debug helper behind pyVoxelFEM's
+// MultigridSolver.smoothing, VoxelFEM.cc:99-104): ONE warp walks the nodes in index order (reverse order for a
+// backward sweep).  Not on the solve path - the cycles use the multicoloured sweep.
+template <int N>
+__global__ void __launch_bounds__(32) gsSerialKernel(Grid<N> g, K0Param<N> K, const Real *__restrict__ Ey, const Real *__restrict__ S, Real *u,
+                                                     const Real *__restrict__ b, const uint8_t *__restrict__ dmask, int forward) {
+    const int lane = threadIdx.x;
+    StencilLane<N> sl; sl.init(g, lane);
+    for (int n_ = 0; n_ < g.nn; ++n_) {
+        const int n = forward ? n_ : g.nn - 1 - n_;
+        Real acc[N], M[N * N];
+        if (S) { // assembled level: the warp forms the row sums, the diagonal block is stencil slot 3^N / 2
+            stencilWarpRow<N, true>(sl, g.nn * N, S, u, n, lane, acc);
+#pragma unroll
+            for (int i = 0; i < N * N; ++i) M[i] = S[stencilIndex<N>(n, ipow3(N) / 2, i)];
+        } else if (lane == 0) {
+            int idx[N]; unflattenNode<N>(g, n, idx);
+#pragma unroll
+            for (int c = 0; c < N; ++c) acc[c] = 0.0;
+#pragma unroll
+            for (int i = 0; i < N * N; ++i) M[i] = 0.0;
+            fineNodeRow<N, true, true>(g, K, Ey, u, idx, acc, M);
+        }
+        if (lane == 0) {
+            Real tt[N];
+#pragma unroll
+            for (int c = 0; c < N; ++c) tt[c] = b[size_t(n) * N + c] - acc[c];
+            gsNodeUpdate<N>(tt, M, dmask[n], forward != 0, u, n);
+            __threadfence();
+        }
+        __syncwarp();
+    }
+}
 
 // ---- warp-per-node kernels for the assembled levels: persistent warps striding over the nodes ----
 constexpr int kWarpBlock = 256; // 8 warps per block

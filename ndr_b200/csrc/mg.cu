@@ -325,6 +325,15 @@ void MG<N>::smoothColoured(size_t l, Real *u, const Real *b, bool forward) {
 }
 
 template <int N>
+void MG<N>::smoothSerial(size_t l, Real *u, const Real *b, bool forward) {
+    if (slab()) throw std::runtime_error("serial Gauss-Seidel is not available on a slab-decomposed grid");
+    const Level &L = lv.at(l);
+    if (l + 1 == lv.size()) throw std::runtime_error("smoothing: the coarsest level is solved exactly (no operator rows are kept for it)");
+    gsSerialKernel<N><<<1, 32, 0, stream>>>(L.g, sim->K0, l == 0 ? sim->moduli() : nullptr, l == 0 ? nullptr : L.S.p, u, b, maskOf(*this, l), forward ? 1 : 0);
+    VFEM_CHECK_LAUNCH(); countLaunch();
+}
+
+template <int N>
 void MG<N>::smooth(size_t l, Real *u, const Real *b, bool forward, size_t sweeps) {
     if (l == 0 || !fusedSweeps || sweeps == 0) { for (size_t i = 0; i < sweeps; ++i) smoothColoured(l, u, b, forward); return; }
     const Level &L = lv.at(l);

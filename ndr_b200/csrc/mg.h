@@ -109,6 +109,7 @@ struct MG : MGBase {
     void computeResidual(size_t l, const Real *u, const Real *b, Real *r);             // MG.hh:401-413
     void applyKMasked(size_t l, const Real *u, Real *out);
     void smoothColoured(size_t l, Real *u, const Real *b, bool forward);               // MG.hh:336-340
+    void smoothSerial(size_t l, Real *u, const Real *b, bool forward);                 // MG.hh:269-282 (lexicographic; debug helper)
     void smooth(size_t l, Real *u, const Real *b, bool forward, size_t sweeps);        // `sweeps` x smoothColoured, fused on the assembled levels
     int sweepGridBlocks = 0;                             // co-resident blocks of gsStencilSweepKernel (cooperative launch)
     void restriction(size_t lf, const Real *vf, Real *bc);                             // MG.hh:145-180

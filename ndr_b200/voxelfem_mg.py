@@ -163,8 +163,13 @@ class MultigridSolver:
         return (out, its.value, rn.value) if return_info else out
 
     def smoothing(self, l, u, b):
-        raise RuntimeError("serial lexicographic Gauss-Seidel (a debug helper of the reference, VoxelFEM.cc:99-104) is not part "
-                           "of the device path; use smoothingMulticoloredGS")
+        """Serial lexicographic Gauss-Seidel on a copy of u, after updateElementStiffnessMatrices (VoxelFEM.cc:99-104,
+        MG.hh:269-282) - a debug helper of the reference; the cycles use smoothingMulticoloredGS."""
+        self.updateElementStiffnessMatrices()
+        out = _np(u).copy().reshape(self._shape(l))
+        ab = _Arg(b, self._n(l))
+        check(lib().vfem_mg_smooth_serial(self._h, l, _ptr(out), ab.ptr, 1, HOST))
+        return out
 
     def debugMulticolorVisit(self):
         """Visit order of the multicoloured sweep (MG.hh:328-334): colours in row-major local-node order."""

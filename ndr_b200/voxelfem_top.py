@@ -68,9 +68,83 @@ class PythonFilter(_Filter):
         self._c_cb = FILTER_CB(_cb)
 
 
-class LangelaarFilter(_Filter):
+class LangelaarFilter(PythonFilter):
+    """Overhang (additive-manufacturing) filter of Langelaar (TopologyOptimizationFilter.hh:164-278): layers along the LAST
+    grid axis, layer 0 on the baseplate; a voxel's density is the smooth minimum of its blueprint density and the smooth
+    maximum (P-norm, P = 40, Q = P - 1.58) of its supporting region (voxel below + in-layer neighbours of that voxel).
+    Sequential over layers and outside every shipped run: evaluated on the host (numpy, vectorised per layer) through the
+    callback-filter slot of the device problem.  The reference's back-propagation takes its layer count from gridDims[1]
+    (Filter.hh:216-218) where apply uses gridDims[N-1]; that quirk is mirrored (identical in 2-D)."""
+    _eps, _P, _Q = 1e-4, 40.0, 40.0 - 1.58
+
     def __init__(self):
-        raise RuntimeError("LangelaarFilter is outside the device hot path (SURVEY 8f row 4)")
+        super().__init__()
+        self.apply_cb, self.backprop_cb = self._apply, self._backprop
+        self._smax = self._filtered = None
+
+    def _support(self, a):
+        """values of the supporting voxels of every voxel of the next layer: list of (array, validity mask or None)"""
+        out = [(a, None)]
+        for d in range(a.ndim):
+            for sh in (-1, 1):
+                r = np.roll(a, -sh, axis=d)
+                m = np.ones(a.shape, bool)
+                idx = [slice(None)] * a.ndim
+                idx[d] = 0 if sh == -1 else -1
+                m[tuple(idx)] = False
+                out.append((r, m))
+        return out
+
+    def _psum(self, layer):
+        tot = np.zeros(layer.shape)
+        for v, m in self._support(layer):
+            tot += np.power(v, self._P) if m is None else np.where(m, np.power(v, self._P), 0.0)
+        return tot
+
+    def _smin(self, x1, x2):
+        return 0.5 * (x1 + x2 - np.sqrt((x1 - x2) ** 2 + self._eps) + np.sqrt(self._eps))
+
+    def _apply(self, xin, xout):
+        if self._dims is None:
+            raise RuntimeError("Grid dimensions must be set before filter can be used")
+        dims = tuple(self._dims)
+        x = xin.reshape(dims)
+        out = np.empty(dims)
+        smax = np.ones(dims)
+        out[..., 0] = x[..., 0]
+        for L in range(1, dims[-1]):
+            smax[..., L] = np.power(self._psum(out[..., L - 1]), 1.0 / self._Q)
+            out[..., L] = self._smin(x[..., L], smax[..., L])
+        self._smax, self._filtered = smax, out.copy()
+        xout[:] = out.ravel()
+
+    def _backprop(self, din, vars_, dout):
+        dims = tuple(self._dims)
+        if self._smax is None:
+            raise RuntimeError("LangelaarFilter.backprop needs a preceding apply")
+        if len(dims) > 2 and dims[1] > dims[-1]:
+            raise RuntimeError("NDVector has no layer %d." % (dims[1] - 1))   # the reference's gridDims[1] quirk (Filter.hh:216)
+        nl = dims[1]
+        d, v, f, sm = din.reshape(dims), vars_.reshape(dims), self._filtered, self._smax
+        lam = np.zeros(dims)
+        ds2 = lambda x1, x2: 0.5 * (1 + (x1 - x2) / np.sqrt((x1 - x2) ** 2 + self._eps))
+        ds1 = lambda x1, x2: 0.5 * (1 - (x1 - x2) / np.sqrt((x1 - x2) ** 2 + self._eps))
+        for L in range(nl - 1, -1, -1):
+            lam[..., L] = d[..., L]
+            if L < nl - 1:
+                A = lam[..., L + 1] * ds2(v[..., L + 1], sm[..., L + 1]) * (self._P / self._Q) * np.power(self._psum(f[..., L]), 1.0 / self._Q - 1.0)
+                fp = np.power(f[..., L], self._P - 1.0)
+                lam[..., L] += A * fp                                   # the voxel below
+                for ax in range(A.ndim):                                # its in-layer neighbours
+                    for sh in (-1, 1):
+                        src = [slice(None)] * A.ndim
+                        dst = [slice(None)] * A.ndim
+                        src[ax] = slice(1, None) if sh == -1 else slice(None, -1)
+                        dst[ax] = slice(None, -1) if sh == -1 else slice(1, None)
+                        lam[..., L][tuple(dst)] += A[tuple(src)] * fp[tuple(dst)]
+        res = np.zeros(dims)
+        res[..., :nl] = (lam * ds1(v, sm))[..., :nl]
+        dout[:] = res.ravel()
 
 
 class TotalVolumeConstraint:

@@ -117,3 +117,54 @@ def test_getk_and_constant_strain_load(oracle_mod):
     g.E_min, g.gamma = 0.0, 1.0  # E(rho) = rho: the density-weighted operator of constantStrainLoad
     pos = np.array([g.nodePosition(i) for i in range(g.numNodes())])
     assert rel(g.constantStrainLoad(eps), g.applyK(pos @ eps.T)) < 1e-12
+
+
+@pytest.mark.parametrize("dim,dom,grid,bc,levels", [(3, [2, 1, 1], [16, 8, 8], "3d/cantilever_flexion.bc", 2), (2, [3, 1], [48, 16], "2d/mbb_beam.bc", 2)])
+def test_serial_smoothing_binding(oracle_mod, dim, dom, grid, bc, levels):
+    """MultigridSolver.smoothing(l, u, b): serial lexicographic Gauss-Seidel (VoxelFEM.cc:99-104, MG.hh:269-282) vs the oracle"""
+    import ndr_b200.pyVoxelFEM as V
+    o = oracle_mod.OracleSim([0] * dim, dom, grid)
+    o.read_material(MATERIAL)
+    g = V.TensorProductSimulator([1] * dim, [np.zeros(dim), np.array(dom, float)], grid)
+    g.readMaterial(MATERIAL)
+    rho = np.random.default_rng(88).uniform(0, 1, o.ne)
+    o.set_densities(rho); g.setElementDensities(rho)
+    o.apply_bc_file(bc_path(bc)); g.applyDisplacementsAndLoadsFromFile(bc_path(bc))
+    o.set_simp(1.0, 1e-4, 3.0)
+    g.E_0, g.E_min, g.gamma = 1.0, 1e-4, 3.0
+    o.mg_create(levels); mg = g.multigridSolver(levels)
+    o.mg_update_stiffness(); o.mg_update_blockks()
+    rng = np.random.default_rng(5)
+    for l in range(levels):
+        nn = o.mg_level_nodes(l)
+        u, b = rng.standard_normal((nn, dim)), rng.standard_normal((nn, dim))
+        assert rel(mg.smoothing(l, u, b), o.mg_smooth(l, u, b, forward=True, serial=True)) < 1e-12, l
+
+
+def test_langelaar_filter_in_the_problem():
+    """LangelaarFilter (Filter.hh:164-278) as a filter of a device TopologyOptimizationProblem: overhang-free densities,
+    gradient chain consistent with finite differences of the filtered objective (away from layer 0, where the reference's
+    back-propagation applies dsmin_dx1(x, 1) although the layer is copied unchanged)."""
+    import ndr_b200.pyVoxelFEM as V
+    g = V.TensorProductSimulator([1, 1], [np.zeros(2), np.array([2.0, 1.0])], [16, 8])
+    g.readMaterial(MATERIAL)
+    g.setUniformDensities(0.5)
+    g.applyDisplacementsAndLoadsFromFile(bc_path("2d/mbb_beam.bc"))
+    g.E_0, g.E_min, g.gamma = 1.0, 1e-4, 3.0
+    obj = V.MultigridComplianceObjective(g.multigridSolver(2))
+    obj.tol = 1e-12
+    lf = V.LangelaarFilter()
+    top = V.TopologyOptimizationProblem(g, obj, [V.TotalVolumeConstraint(0.5)], [lf])
+    x = np.random.default_rng(2).uniform(0.3, 0.9, g.numElements())
+    top.setVars(x)
+    phys = top.getDensities().reshape(16, 8)
+    ref = np.empty(x.size); lf2 = V.LangelaarFilter(); lf2._dims = [16, 8]; lf2.apply_cb(x, ref)
+    np.testing.assert_allclose(phys.ravel(), ref, rtol=0, atol=1e-15)
+    assert np.all(phys[:, 1:] <= np.maximum.reduce([phys[:, :-1], np.roll(phys[:, :-1], 1, 0), np.roll(phys[:, :-1], -1, 0)]) + 0.2)
+    grad = top.evaluateObjectiveGradient().reshape(16, 8)
+    J0 = top.evaluateObjective()
+    for (i, j) in [(3, 2), (8, 4), (12, 6)]:
+        xp = x.copy().reshape(16, 8); xp[i, j] += 1e-5
+        top.setVars(xp.ravel())
+        fd = (top.evaluateObjective() - J0) / 1e-5
+        assert abs(fd - grad[i, j]) <= 2e-3 * abs(grad[i, j]) + 1e-6 * np.max(np.abs(grad)), (i, j, fd, grad[i, j])
