@@ -15,6 +15,7 @@
 // Update rule, colour order and in-node substitution are the reference's; results are bit-identical to gsFineKernel.
 #pragma once
 #include "kernels.cuh"
+#include "async_copy.cuh"
 
 namespace vfem {
 
@@ -26,26 +27,6 @@ constexpr int kGsTilePitch = 3 * (2 * kGsTileTZMax + 1) + 7;                 // 
 constexpr size_t kGsTileSmem = size_t(kGsTileBX) * kGsTileBY * kGsTilePitch * sizeof(Real);
 static_assert(kGsTilePitch % 2 == 0, "row pitch must keep 16-byte alignment");
 static_assert(kGsTileTX * kGsTileTY * kGsTileTZMax <= kGsTileThreads, "one thread per lattice site");
-
-__device__ __forceinline__ unsigned smemAddr(const void *p) { return unsigned(__cvta_generic_to_shared(p)); }
-__device__ __forceinline__ void mbarInit(unsigned long long *bar, unsigned count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smemAddr(bar)), "r"(count) : "memory");
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbarArriveExpectTx(unsigned long long *bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smemAddr(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbarWait(unsigned long long *bar, unsigned phase) {
-    unsigned done = 0;
-    while (!done)
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(done) : "r"(smemAddr(bar)), "r"(phase) : "memory");
-}
-// global -> shared bulk copy (16-byte aligned addresses, size a multiple of 16), completion bytes counted on `bar`
-__device__ __forceinline__ void bulkLoad(void *dst, const void *src, unsigned bytes, unsigned long long *bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smemAddr(dst)), "l"(src), "r"(bytes), "r"(smemAddr(bar)) : "memory");
-}
 
 struct GsTilePlan { dim3 grid; int tz; };
 
@@ -77,20 +58,22 @@ gsFineTileKernel(Grid<3> g, K0Param<3> K, const Real *__restrict__ Ey, Real *u, 
     const int x0 = colourFirstPlane<3>(g, colour) + 2 * lx0, y0 = py + 2 * ly0, z0 = pz + 2 * lz0; // first node of the tile
     const int zLo = z0 - 1, BZ = 2 * tzc + 1;            // node window [zLo, zLo + BZ) of every staged row
 
+    const long long baseOdd = (long long)(reinterpret_cast<size_t>(u) >> 3) & 1;
     if (threadIdx.x == 0) mbarInit(&bar, 32);
     __syncthreads();
     if (threadIdx.x < 32) { // warp 0 stages the rows; every lane arrives once with the bytes of the copies it issued
         unsigned bytes = 0;
         const int za = max(zLo, 0), zb = min(zLo + BZ, nz);
         const long long total = (long long)g.nn * 24;
+        const long long ubase = (long long)reinterpret_cast<size_t>(u);
         for (int r = threadIdx.x; r < BX * BY; r += 32) {
             const int bx = r / BY, by = r - bx * BY;
             const int x = x0 - 1 + bx, y = y0 - 1 + by;
             if (x < 0 || x >= nx || y < 0 || y >= ny) continue;
             const long long row0 = ((long long)x * ny + y) * nz;
             const long long src = (row0 + za) * 24;
-            const int delta = int(src & 8);
-            const int orow = 2 + int((row0 + z0 + 1) & 1);          // rowParity: see the readers below
+            const int delta = int((ubase + src) & 8);               // u itself may be only 8-byte aligned (a view into a larger field)
+            const int orow = 2 + int((baseOdd + row0 + z0 + 1) & 1); // rowParity: see the readers below
             Real *dst = box + r * RP + orow + 3 * (za - zLo) - (delta >> 3);
             const int need = (zb - za) * 24 + delta;
             int size = (need + 15) & ~15;
@@ -133,7 +116,7 @@ gsFineTileKernel(Grid<3> g, K0Param<3> K, const Real *__restrict__ Ey, Real *u, 
 
     // row (x + dx, y + dy) was staged at offset 2 + ((row0 + z0 + 1) & 1): the parity that makes its first node's
     // shared-memory address congruent (mod 16) to its global address
-    const int p0 = int((((long long)x * ny + y) * nz + z0 + 1) & 1), fx = (ny * nz) & 1, fy = nz & 1;
+    const int p0 = int((baseOdd + ((long long)x * ny + y) * nz + z0 + 1) & 1), fx = (ny * nz) & 1, fy = nz & 1;
     // neighbour-major accumulation: node k's three values are read from the tile once and folded into the running rows of
     // every incident element that contains it (8 elements x 3 rows of accumulators instead of the whole 27-node neighbourhood
     // in registers).  Per element the terms arrive in the same order as in fineNodeRowCompute, so the sums are bit-identical.

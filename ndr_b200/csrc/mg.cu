@@ -290,10 +290,10 @@ template <int N> void MG<N>::applyK(size_t l, const Real *u, Real *out) { applyM
 template <int N> void MG<N>::computeResidual(size_t l, const Real *u, const Real *b, Real *r) { applyMode<1>(l, u, b, r); }
 template <int N> void MG<N>::applyKMasked(size_t l, const Real *u, Real *out) { applyMode<2>(l, u, nullptr, out); }
 
-// 3-D fine level: shared-memory tile kernel (gs_tile.cuh); needs a 16-byte aligned u for its bulk copies
+// 3-D fine level: shared-memory tile kernel (gs_tile.cuh)
 static inline bool launchGsFineTile(const Grid<3> &g, const K0Param<3> &K, const Real *Ey, Real *u, const Real *b, const uint8_t *dmask,
                                     int colour, int forward, cudaStream_t stream) {
-    if (reinterpret_cast<size_t>(u) & 15) return false;
+    if (reinterpret_cast<size_t>(u) & 7) return false;
     const GsTilePlan p = planGsTile(g, colour);
     gsFineTileKernel<3><<<p.grid, kGsTileThreads, kGsTileSmem, stream>>>(g, K, Ey, u, b, dmask, colour, forward, p.tz);
     return true;

@@ -3,6 +3,7 @@
 #include "kernels.cuh"
 #include "kernels_vec.cuh"
 #include "block_tri.h"
+#include "apply_march_tma.cuh"
 
 namespace vfem {
 
@@ -305,9 +306,11 @@ void Sim<N>::applyFineRange(const Real *u, const Real *b, const uint8_t *mask, R
             plan = &it->second;
         }
     }
-    if (useMarch())
-        launchApplyMarch<MODE>(reinterpret_cast<const Grid<3> &>(gv), Khat, khatStructure == 2 && applyVariant != 2, *plan, Ey, u, b, mask, out, st,
-                               edgeSkip);
+    if (useMarch() && applyVariant != 4)   // ring-fed marching kernel (apply_march_tma.cuh)
+        launchApplyMarchTma<MODE>(reinterpret_cast<const Grid<3> &>(gv), Khat, khatStructure == 2 && applyVariant != 2, *plan, Ey, u, b, mask, out, st,
+                                  edgeSkip);
+    else if (useMarch())                   // variant 4: first-generation marching kernel (per-thread global loads, CTA barrier per plane)
+        launchApplyMarch<MODE>(reinterpret_cast<const Grid<3> &>(gv), Khat, khatStructure == 2, *plan, Ey, u, b, mask, out, st, edgeSkip);
     else
         applyFineKernel<N, MODE><<<(gv.nn + kBlock - 1) / kBlock, kBlock, 0, st>>>(gv, K0, Ey, u, b, mask, out, edgeSkip);
     VFEM_CHECK_LAUNCH(); countLaunch();

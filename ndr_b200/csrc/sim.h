@@ -32,7 +32,7 @@ struct Sim : SimBase {
     KhatParam Khat;
     int khatStructure = 0;             // 0: not block diagonal -> gather kernel; 1: dense blocks; 2: isotropic pattern
     MarchPlan marchPlan;
-    int applyVariant = 0;              // 0 = auto (marching kernel when K0 allows it), 1 = per-node gather kernel, 2 = marching kernel with dense 3x3 blocks
+    int applyVariant = 0;              // 0 = auto (ring-fed marching kernel when K0 allows it), 1 = per-node gather kernel, 2 = marching kernel with dense 3x3 blocks, 4 = first-generation marching kernel
     bool useMarch() const { return N == 3 && khatStructure > 0 && applyVariant != 1; }
 
     // boundary data (host mirrors; device copies refreshed lazily)
