@@ -27,29 +27,32 @@ struct FactorParams {
     int pn[N > 1 ? N - 1 : 1];      // nodes per in-plane axis (axes 1..N-1 of the grid)
 };
 
-// in-plane neighbours of dof i = (node a, component): calls f(j) for every dof j of the nodes within +-1 of a
-template <int N, class F>
-__device__ __forceinline__ void forPlaneNeighbours(const FactorParams<N> &fp, int i, F f) {
+constexpr int planeNeighbourMax(int N) { return ipow3(N - 1) * N; }
+
+// in-plane neighbours of dof i = (node a, component): the dofs of the nodes within +-1 of a; slot s of the fixed-size list
+// is -1 where the neighbour lies outside the plane
+template <int N>
+__device__ __forceinline__ void planeNeighbours(const FactorParams<N> &fp, int i, int (&nb)[planeNeighbourMax(N)]) {
     const int a = i / N;
     if (N == 2) {
+#pragma unroll
         for (int d = -1; d <= 1; ++d) {
             const int y = a + d;
-            if (y < 0 || y >= fp.pn[0]) continue;
+            const bool ok = y >= 0 && y < fp.pn[0];
 #pragma unroll
-            for (int c = 0; c < N; ++c) f(y * N + c);
+            for (int c = 0; c < N; ++c) nb[(d + 1) * N + c] = ok ? y * N + c : -1;
         }
     } else {
         const int nz = fp.pn[N - 2], y = a / nz, z = a - y * nz;
-        for (int dy = -1; dy <= 1; ++dy) {
-            const int yy = y + dy;
-            if (yy < 0 || yy >= fp.pn[0]) continue;
-            for (int dz = -1; dz <= 1; ++dz) {
-                const int zz = z + dz;
-                if (zz < 0 || zz >= nz) continue;
 #pragma unroll
-                for (int c = 0; c < N; ++c) f((yy * nz + zz) * N + c);
+        for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+            for (int dz = -1; dz <= 1; ++dz) {
+                const int yy = y + dy, zz = z + dz;
+                const bool ok = yy >= 0 && yy < fp.pn[0] && zz >= 0 && zz < nz;
+#pragma unroll
+                for (int c = 0; c < N; ++c) nb[((dy + 1) * 3 + dz + 1) * N + c] = ok ? (yy * nz + zz) * N + c : -1;
             }
-        }
     }
 }
 
@@ -95,10 +98,31 @@ __device__ __forceinline__ void gaussJordanInvert(Real *M, int P, int cb, int nc
             // ---- trailing tiles (i, j), i != kb, j != kb:  C -= (F_i D^-1) R_j ----
             const int nt = (nbk - 1) * (nbk - 1);
             const int t0 = int((long long)cb * nt / ncb), t1 = int((long long)(cb + 1) * nt / ncb);
-            int curI = -1;
-            for (int t = t0; t < t1; ++t) {
+            // the R tile and the C entries of the NEXT tile are fetched into registers before the arithmetic of the current
+            // one (a tile is 3 dependent L2 round trips otherwise: the loop is latency-, not FP64-bound)
+            auto tileOf = [&](int t, int &i, int &j) {
                 const int ii = t / (nbk - 1), jj = t - ii * (nbk - 1);
-                const int i = ii + (ii >= kb), j = jj + (jj >= kb);
+                i = ii + (ii >= kb); j = jj + (jj >= kb);
+            };
+            auto fetchR = [&](int j, Real (&rr)[4]) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int e = tid + q * kFactorThreads, r = k0 + (e & 31), c = j * kFB + (e >> 5);
+                    rr[q] = (r < P && c < P) ? __ldcg(M + size_t(r) + size_t(c) * P) : 0.0;
+                }
+            };
+            auto fetchC = [&](int i, int j, Real (&cv)[4]) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int r = i * kFB + tr, c = j * kFB + 4 * tc + q;
+                    cv[q] = (r < P && c < P) ? __ldcg(M + size_t(r) + size_t(c) * P) : 0.0;
+                }
+            };
+            int curI = -1, i = 0, j = 0;
+            Real rr[4], cn[4];
+            if (t0 < t1) { tileOf(t0, i, j); fetchR(j, rr); fetchC(i, j, cn); }
+            for (int t = t0; t < t1; ++t) {
+                tileOf(t, i, j);
                 __syncthreads();
                 if (i != curI) {
                     loadTile(sF, i * kFB, k0, false);
@@ -114,7 +138,10 @@ __device__ __forceinline__ void gaussJordanInvert(Real *M, int P, int cb, int nc
                     for (int q = 0; q < 4; ++q) sG[tr][4 * tc + q] = g[q];
                     curI = i;
                 }
-                loadTile(sR, k0, j * kFB, false);
+                Real cv[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) { const int e = tid + q * kFactorThreads; sR[e & 31][e >> 5] = rr[q]; cv[q] = cn[q]; }
+                if (t + 1 < t1) { int i2, j2; tileOf(t + 1, i2, j2); fetchR(j2, rr); fetchC(i2, j2, cn); }
                 __syncthreads();
                 const int r = i * kFB + tr;
                 Real acc[4] = {0.0, 0.0, 0.0, 0.0};
@@ -127,7 +154,7 @@ __device__ __forceinline__ void gaussJordanInvert(Real *M, int P, int cb, int nc
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int c = j * kFB + 4 * tc + q;
-                    if (r < P && c < P) { Real *m = M + size_t(r) + size_t(c) * P; *m = __ldcg(m) - acc[q]; }
+                    if (r < P && c < P) M[size_t(r) + size_t(c) * P] = cv[q] - acc[q];
                 }
             }
         }
@@ -182,7 +209,8 @@ static __global__ void __launch_bounds__(kFactorThreads) blockTriFactorKernel(Fa
     const int c = (G >= 2 && int(blockIdx.x) >= Gh && int(blockIdx.x) < 2 * Gh) ? 1 : 0;
     const bool spare = G >= 2 && int(blockIdx.x) >= 2 * Gh;
     const int ncb = G >= 2 ? Gh : 1, cb = G >= 2 ? int(blockIdx.x) - c * Gh : 0;
-    const long long tthreads = (long long)ncb * kFactorThreads, tt = (long long)cb * kFactorThreads + threadIdx.x;
+    constexpr int NB = planeNeighbourMax(N);
+    const int lane = threadIdx.x & 31, tw = cb * (kFactorThreads / 32) + (threadIdx.x >> 5), tnw = ncb * (kFactorThreads / 32); // warp of the team
     const int S = ci.steps();
     const bool serial = G < 2; // one team walks both chains one after the other
     for (int pass = 0; pass < (serial ? 2 : 1); ++pass) {
@@ -193,18 +221,24 @@ static __global__ void __launch_bounds__(kFactorThreads) blockTriFactorKernel(Fa
             gaussJordanInvert(active ? D + PP * p : nullptr, P, cb, ncb, info, p);
             // ---- T = A S^-1 (chain 0: T_{p+1} = A_{p+1,p} S_p^-1, block p; chain 1: U_{p-1} = A_{p,p-1}^T S_p^-1, block p-1) ----
             const int q = cc == 0 ? p : p - 1;
-            if (active) {
+            if (active) { // one warp per row i of T: its <= 3^(N-1) N coefficients of A first, then lanes over the columns
                 const Real *A = Lo + PP * q, *Si = D + PP * p;
                 Real *tr = Trm + PP * q, *tc = Tcm + PP * q;
-                for (long long e = tt; e < (long long)PP; e += tthreads) {
-                    const int i = int(e % P), k = int(e / P);
-                    Real acc = 0.0;
-                    forPlaneNeighbours<N>(fp, i, [&](int j) {
-                        const Real a = cc == 0 ? A[size_t(i) + size_t(j) * P] : A[size_t(j) + size_t(i) * P];
-                        acc = fma(a, __ldcg(Si + size_t(j) + size_t(k) * P), acc);
-                    });
-                    tc[size_t(i) + size_t(k) * P] = acc;
-                    tr[size_t(i) * P + k] = acc;
+                for (int i = tw; i < P; i += tnw) {
+                    int nb[NB]; Real av[NB];
+                    planeNeighbours<N>(fp, i, nb);
+#pragma unroll
+                    for (int m = 0; m < NB; ++m) av[m] = nb[m] < 0 ? 0.0 : (cc == 0 ? A[size_t(i) + size_t(nb[m]) * P] : A[size_t(nb[m]) + size_t(i) * P]);
+                    for (int k = lane; k < P; k += 32) {
+                        Real sv[NB];
+#pragma unroll
+                        for (int m = 0; m < NB; ++m) sv[m] = nb[m] < 0 ? 0.0 : __ldcg(Si + size_t(k) + size_t(nb[m]) * P); // S^-1 is symmetric: (j,k) read as (k,j)
+                        Real acc = 0.0;
+#pragma unroll
+                        for (int m = 0; m < NB; ++m) acc = fma(av[m], sv[m], acc);
+                        tr[size_t(i) * P + k] = acc;
+                        tc[size_t(i) + size_t(k) * P] = acc;
+                    }
                 }
             }
             grid.sync();
@@ -213,18 +247,24 @@ static __global__ void __launch_bounds__(kFactorThreads) blockTriFactorKernel(Fa
             for (int turn = 0; turn < 2; ++turn) {
                 const bool clash = !serial && s == ci.len(0) - 1 && s == ci.len(1) - 1; // both targets are `mid` in this step
                 if (turn == 1 && !clash) break;
-                if (active && (clash ? turn == cc : turn == 0)) {
+                if (active && (clash ? turn == cc : turn == 0)) { // one warp per column k of the target block, lanes over its rows
                     const Real *A = Lo + PP * q, *T = Tcm + PP * q;
                     Real *Dn = D + PP * target;
-                    for (long long e = tt; e < (long long)PP; e += tthreads) {
-                        const int i = int(e % P), k = int(e / P);
-                        Real acc = 0.0;
-                        forPlaneNeighbours<N>(fp, k, [&](int j) {
-                            const Real a = cc == 0 ? A[size_t(k) + size_t(j) * P] : A[size_t(j) + size_t(k) * P];
-                            acc = fma(__ldcg(T + size_t(i) + size_t(j) * P), a, acc);
-                        });
-                        Real *d = Dn + size_t(i) + size_t(k) * P;
-                        *d = __ldcg(d) - acc;
+                    for (int k = tw; k < P; k += tnw) {
+                        int nb[NB]; Real av[NB];
+                        planeNeighbours<N>(fp, k, nb);
+#pragma unroll
+                        for (int m = 0; m < NB; ++m) av[m] = nb[m] < 0 ? 0.0 : (cc == 0 ? A[size_t(k) + size_t(nb[m]) * P] : A[size_t(nb[m]) + size_t(k) * P]);
+                        for (int i = lane; i < P; i += 32) {
+                            Real tv[NB];
+#pragma unroll
+                            for (int m = 0; m < NB; ++m) tv[m] = nb[m] < 0 ? 0.0 : __ldcg(T + size_t(i) + size_t(nb[m]) * P);
+                            Real *d = Dn + size_t(i) + size_t(k) * P;
+                            Real acc = __ldcg(d);
+#pragma unroll
+                            for (int m = 0; m < NB; ++m) acc = fma(-tv[m], av[m], acc);
+                            *d = acc;
+                        }
                     }
                 }
                 grid.sync();

