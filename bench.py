@@ -484,6 +484,14 @@ def extra_configs(args, V, S, torch, dist, L, rank, world, local, hbm_peak, peak
             out[name] = {"error": "%s: %s" % (type(e).__name__, e)}
             if world > 1:
                 raise
+    if world == 1:  # BASELINE configs[4]: one neural-design step (MLP forward, VoxelFEM solve + gradient, backward, Adam) at 256x128x128
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import neural_loop
+            out["neural_loop_256x128x128"] = neural_loop.run([256, 128, 128], steps=3)
+            torch.cuda.empty_cache()
+        except Exception as e:  # noqa: BLE001
+            out["neural_loop_256x128x128"] = {"error": "%s: %s" % (type(e).__name__, e)}
     return out
 
 

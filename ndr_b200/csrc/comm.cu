@@ -219,7 +219,7 @@ void newNcclUniqueId(uint8_t *out128) {
 std::shared_ptr<SlabComm> makeNcclComm(const uint8_t *uniqueId128, int rank, int world) {
     auto c = std::make_shared<NcclComm>();
     c->rank = rank; c->world = world;
-    c->graphs = getenv("VFEM_SLAB_GRAPH") != nullptr;
+    c->graphs = getenv("VFEM_SLAB_NO_GRAPH") == nullptr; // ncclSend / ncclRecv / ncclAllReduce are graph-capturable (NCCL >= 2.9): the slab preconditioner replays as one graph
     ncclUniqueId id;
     memcpy(&id, uniqueId128, 128);
     VFEM_NCCL(nccl().CommInitRank(&c->comm, world, id, rank));

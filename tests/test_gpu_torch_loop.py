@@ -52,3 +52,16 @@ def test_device_arrays_are_used_in_place(oracle_mod):
     top.evaluateObjectiveGradient(out=gd); top.getDensities(out=dd)
     np.testing.assert_allclose(gd.cpu().numpy(), gr, rtol=0, atol=1e-8 * np.max(np.abs(gr)))
     np.testing.assert_array_equal(dd.cpu().numpy(), dens)
+
+
+def test_fourier_feature_mlp_design_step():
+    """BASELINE configs[4] in small: a Fourier-feature MLP (architecture of networks.py:128-185) drives VoxelFEMFunction on the
+    GPU; Adam steps run end to end (tools/neural_loop.py) and the compliance gradient reaches the network weights."""
+    import os, sys
+    from conftest import ROOT
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import neural_loop
+    r = neural_loop.run([32, 16, 16], steps=4, levels=2)
+    assert r["elements"] == 32 * 16 * 16 and len(r["compliance_history"]) == 4
+    assert all(np.isfinite(r["compliance_history"])) and r["pcg_iterations_last"] > 0
+    assert r["compliance_history"][-1] != r["compliance_history"][0]   # the weights moved
