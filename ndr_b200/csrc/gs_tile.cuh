@@ -19,33 +19,37 @@
 
 namespace vfem {
 
-constexpr int kGsTileTX = 2, kGsTileTY = 2;       // lattice sites per CTA along axes 0 and 1
-constexpr int kGsTileTZMax = 34;                  // ... and at most this many along axis 2
-constexpr int kGsTileThreads = 160;               // >= TX * TY * TZMax = 136
-constexpr int kGsTileBX = 2 * kGsTileTX + 1, kGsTileBY = 2 * kGsTileTY + 1;
-constexpr int kGsTilePitch = 3 * (2 * kGsTileTZMax + 1) + 7;                 // doubles per staged row (even: rows stay 16-byte aligned)
-constexpr size_t kGsTileSmem = size_t(kGsTileBX) * kGsTileBY * kGsTilePitch * sizeof(Real);
-static_assert(kGsTilePitch % 2 == 0, "row pitch must keep 16-byte alignment");
-static_assert(kGsTileTX * kGsTileTY * kGsTileTZMax <= kGsTileThreads, "one thread per lattice site");
+constexpr int kGsTileTZMax = 34;                  // lattice sites per CTA along axis 2 (at most)
+template <int TX_, int TY_>
+struct GsTileCfg {
+    static constexpr int TX = TX_, TY = TY_;      // lattice sites per CTA along axes 0 and 1
+    static constexpr int NT = (TX * TY * kGsTileTZMax + 31) / 32 * 32;   // one thread per lattice site
+    static constexpr int BX = 2 * TX + 1, BY = 2 * TY + 1;
+    static constexpr int PITCH = 3 * (2 * kGsTileTZMax + 1) + 7;         // doubles per staged row (even: rows stay 16-byte aligned)
+    static constexpr size_t SMEM = size_t(BX) * BY * PITCH * sizeof(Real);
+    static constexpr int MINB = (NT <= 96) ? 5 : (NT <= 160) ? 3 : 2;    // resident CTAs per SM the register budget is sized for
+    static_assert(PITCH % 2 == 0, "row pitch must keep 16-byte alignment");
+};
 
 struct GsTilePlan { dim3 grid; int tz; };
 
 // tiles of the colour lattice (restricted to the owned planes of axis 0)
+template <class Cfg>
 inline GsTilePlan planGsTile(const Grid<3> &g, int colour) {
     const int cx = colourPlaneCount<3>(g, colour);
     const int cy = (g.n[1] - 1 - ((colour >> 1) & 1)) / 2 + 1, cz = (g.n[2] - 1 - (colour & 1)) / 2 + 1;
     GsTilePlan p;
     const int ntz = (cz + kGsTileTZMax - 1) / kGsTileTZMax;
     p.tz = (cz + ntz - 1) / ntz;
-    p.grid = dim3(unsigned(ntz), unsigned((cy + kGsTileTY - 1) / kGsTileTY), unsigned((cx + kGsTileTX - 1) / kGsTileTX));
+    p.grid = dim3(unsigned(ntz), unsigned((cy + Cfg::TY - 1) / Cfg::TY), unsigned((cx + Cfg::TX - 1) / Cfg::TX));
     return p;
 }
 
-template <int MINB>
-__global__ void __launch_bounds__(kGsTileThreads, MINB)
+template <class Cfg>
+__global__ void __launch_bounds__(Cfg::NT, Cfg::MINB)
 gsFineTileKernel(Grid<3> g, K0Param<3> K, const Real *__restrict__ Ey, Real *u, const Real *__restrict__ b,
                  const uint8_t *__restrict__ dmask, int colour, int forward, int tz) {
-    constexpr int TX = kGsTileTX, TY = kGsTileTY, BX = kGsTileBX, BY = kGsTileBY, RP = kGsTilePitch;
+    constexpr int TX = Cfg::TX, TY = Cfg::TY, BX = Cfg::BX, BY = Cfg::BY, RP = Cfg::PITCH;
     extern __shared__ __align__(16) unsigned char gsTileRaw[];
     Real *box = reinterpret_cast<Real *>(gsTileRaw);
     __shared__ __align__(8) unsigned long long bar;
@@ -124,25 +128,43 @@ gsFineTileKernel(Grid<3> g, K0Param<3> K, const Real *__restrict__ Ey, Real *u, 
 #pragma unroll
     for (int s = 0; s < 8; ++s) re[s][0] = re[s][1] = re[s][2] = 0.0;
 #pragma unroll
-    for (int k = 0; k < 27; ++k) {
-        const int dx = k / 9 - 1, dy = (k / 3) % 3 - 1, dz = k % 3 - 1;
-        const bool ok = (x + dx >= 0) && (x + dx < nx) && (y + dy >= 0) && (y + dy < ny) && (z + dz >= 0) && (z + dz < nz);
+    for (int r = 0; r < 9; ++r) {
+        const int dx = r / 3 - 1, dy = r % 3 - 1;
+        // the three z-neighbours of row (dx, dy) are 9 contiguous doubles starting at an index of the row's parity (the same for
+        // every thread of the CTA: x, y advance in steps of 2): four aligned 16-byte loads + one 8-byte load instead of nine
+        // 8-byte loads that conflict 2-way at the 48-byte lane stride
         const int par = p0 ^ (dx != 0 ? fx : 0) ^ (dy != 0 ? fy : 0);
-        const Real *row = box + ((2 * lx + 1 + dx) * BY + (2 * ly + 1 + dy)) * RP + 2 + par + (2 * lz + 1 + dz) * 3;
-        Real v[3];
+        const Real *row = box + ((2 * lx + 1 + dx) * BY + (2 * ly + 1 + dy)) * RP + 2 + 6 * lz; // even index: 16-byte aligned
+        Real w[9];
+        if (par) {
+            w[0] = row[1];
 #pragma unroll
-        for (int c = 0; c < 3; ++c) v[c] = ok ? row[c] : 0.0;
-        if (k == 13) { uc[0] = v[0]; uc[1] = v[1]; uc[2] = v[2]; }
+            for (int i = 0; i < 4; ++i) { const double2 t2 = *reinterpret_cast<const double2 *>(row + 2 + 2 * i); w[1 + 2 * i] = t2.x; w[2 + 2 * i] = t2.y; }
+        } else {
 #pragma unroll
-        for (int s = 0; s < 8; ++s) { // incident element s holds this node at offset sd - 1 + qd = dd  =>  qd = dd + 1 - sd in {0, 1}
-            const int s0 = (s >> 2) & 1, s1 = (s >> 1) & 1, s2 = s & 1;
-            const int q0 = dx + 1 - s0, q1 = dy + 1 - s1, q2 = dz + 1 - s2;
-            if (q0 < 0 || q0 > 1 || q1 < 0 || q1 > 1 || q2 < 0 || q2 > 1) continue;
-            const int q = q0 * 4 + q1 * 2 + q2, loc = ((1 - s0) << 2) | ((1 - s1) << 1) | (1 - s2);
+            for (int i = 0; i < 4; ++i) { const double2 t2 = *reinterpret_cast<const double2 *>(row + 2 * i); w[2 * i] = t2.x; w[2 * i + 1] = t2.y; }
+            w[8] = row[8];
+        }
+        const bool okr = (x + dx >= 0) && (x + dx < nx) && (y + dy >= 0) && (y + dy < ny);
 #pragma unroll
-            for (int bb = 0; bb < 3; ++bb)
+        for (int dzi = 0; dzi < 3; ++dzi) {
+            const int dz = dzi - 1, k = r * 3 + dzi;
+            const bool ok = okr && (z + dz >= 0) && (z + dz < nz);
+            Real v[3];
 #pragma unroll
-                for (int c = 0; c < 3; ++c) re[s][c] = fma(K.k[(loc * 3 + c) * 24 + q * 3 + bb], v[bb], re[s][c]);
+            for (int c = 0; c < 3; ++c) v[c] = ok ? w[dzi * 3 + c] : 0.0;
+            if (k == 13) { uc[0] = v[0]; uc[1] = v[1]; uc[2] = v[2]; }
+#pragma unroll
+            for (int s = 0; s < 8; ++s) { // incident element s holds this node at offset sd - 1 + qd = dd  =>  qd = dd + 1 - sd in {0, 1}
+                const int s0 = (s >> 2) & 1, s1 = (s >> 1) & 1, s2 = s & 1;
+                const int q0 = dx + 1 - s0, q1 = dy + 1 - s1, q2 = dz + 1 - s2;
+                if (q0 < 0 || q0 > 1 || q1 < 0 || q1 > 1 || q2 < 0 || q2 > 1) continue;
+                const int q = q0 * 4 + q1 * 2 + q2, loc = ((1 - s0) << 2) | ((1 - s1) << 1) | (1 - s2);
+#pragma unroll
+                for (int bb = 0; bb < 3; ++bb)
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) re[s][c] = fma(K.k[(loc * 3 + c) * 24 + q * 3 + bb], v[bb], re[s][c]);
+            }
         }
     }
     Real acc[3] = {0.0, 0.0, 0.0}, M[9];

@@ -291,14 +291,26 @@ template <int N> void MG<N>::computeResidual(size_t l, const Real *u, const Real
 template <int N> void MG<N>::applyKMasked(size_t l, const Real *u, Real *out) { applyMode<2>(l, u, nullptr, out); }
 
 // 3-D fine level: shared-memory tile kernel (gs_tile.cuh)
+template <class Cfg>
+static inline void launchGsFineTileCfg(const Grid<3> &g, const K0Param<3> &K, const Real *Ey, Real *u, const Real *b, const uint8_t *dmask,
+                                       int colour, int forward, cudaStream_t stream) {
+    static bool once = (cudaFuncSetAttribute(gsFineTileKernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM)), true);
+    (void)once;
+    const GsTilePlan p = planGsTile<Cfg>(g, colour);
+    gsFineTileKernel<Cfg><<<p.grid, Cfg::NT, Cfg::SMEM, stream>>>(g, K, Ey, u, b, dmask, colour, forward, p.tz);
+}
 static inline bool launchGsFineTile(const Grid<3> &g, const K0Param<3> &K, const Real *Ey, Real *u, const Real *b, const uint8_t *dmask,
-                                    int colour, int forward, cudaStream_t stream) {
+                                    int colour, int forward, cudaStream_t stream, int variant) {
     if (reinterpret_cast<size_t>(u) & 7) return false;
-    const GsTilePlan p = planGsTile(g, colour);
-    gsFineTileKernel<3><<<p.grid, kGsTileThreads, kGsTileSmem, stream>>>(g, K, Ey, u, b, dmask, colour, forward, p.tz);
+    switch (variant) { // lattice sites per CTA along axes 0, 1 (experiment knob VFEM_GS_VARIANT; 1 = default)
+    case 2: launchGsFineTileCfg<GsTileCfg<1, 2>>(g, K, Ey, u, b, dmask, colour, forward, stream); break;
+    case 3: launchGsFineTileCfg<GsTileCfg<2, 4>>(g, K, Ey, u, b, dmask, colour, forward, stream); break;
+    case 4: launchGsFineTileCfg<GsTileCfg<1, 4>>(g, K, Ey, u, b, dmask, colour, forward, stream); break;
+    default: launchGsFineTileCfg<GsTileCfg<2, 2>>(g, K, Ey, u, b, dmask, colour, forward, stream); break;
+    }
     return true;
 }
-static inline bool launchGsFineTile(const Grid<2> &, const K0Param<2> &, const Real *, Real *, const Real *, const uint8_t *, int, int, cudaStream_t) { return false; }
+static inline bool launchGsFineTile(const Grid<2> &, const K0Param<2> &, const Real *, Real *, const Real *, const uint8_t *, int, int, cudaStream_t, int) { return false; }
 
 // Halo traffic of a coloured sweep (slab mode): the colours whose axis-0 parity is even (the first half of the forward
 // order, MG.hh:292-294) only read odd ghost planes and vice versa, and own0 is even / own1 odd on interior faces, so a
@@ -314,7 +326,7 @@ void MG<N>::smoothColoured(size_t l, Real *u, const Real *b, bool forward) {
         if (cnt > 0) {
             const unsigned blocks = unsigned((cnt + kBlock - 1) / kBlock);
             if (l == 0) { // gsVariant 0: one thread per node gathering from global memory (the 2-D path and the fallback)
-                if (!(N == 3 && gsVariant != 0 && launchGsFineTile(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0, stream)))
+                if (!(N == 3 && gsVariant != 0 && launchGsFineTile(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0, stream, gsVariant)))
                     gsFineKernel<N, 4><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
             }
             else gsStencilWarpKernel<N><<<warpGridBlocks(cnt), kWarpBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), colour, forward ? 1 : 0, cnt);

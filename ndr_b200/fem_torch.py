@@ -19,6 +19,10 @@ class VoxelFEMFunction(autograd.Function):
         """densities: predicted physical densities (any float dtype, CPU or CUDA); top: pyVoxelFEM.TopologyOptimizationProblem"""
         x = densities.detach()
         if x.is_cuda:
+            # stream contract (INTEGRATION.md 4): the library works on the legacy default stream, which orders against torch only
+            # while torch's current stream is its default stream
+            if torch.cuda.current_stream(x.device) != torch.cuda.default_stream(x.device):
+                raise RuntimeError("VoxelFEMFunction: call it on torch's default CUDA stream (the solver enqueues on stream 0)")
             x64 = x.reshape(-1).to(torch.float64).contiguous()      # the FP32 -> FP64 cast is the only pass over the data
             top.setVars(x64)                                        # device pointer, no host copy
             objective = 2.0 * top.evaluateObjective()

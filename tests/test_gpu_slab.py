@@ -57,7 +57,7 @@ def make_rank(grid, levels, rank, world, comms, hs, rho):
     return s
 
 
-@pytest.mark.parametrize("grid,levels,world", [([32, 16, 16], 2, 2), ([32, 16, 16], 2, 4), ([48, 16, 16], 3, 3), ([32, 8, 8], 1, 5)])
+@pytest.mark.parametrize("grid,levels,world", [([32, 16, 16], 2, 2), ([32, 16, 16], 2, 4), ([48, 16, 16], 3, 3), ([32, 8, 8], 1, 5), ([64, 32, 32], 3, 2)])
 def test_slab_setup_and_apply(oracle_mod, grid, levels, world):
     """local load vector / Dirichlet mask = windows of the global ones; K u on the owned planes = global K u"""
     from ndr_b200.slab import ThreadHostSum, make_thread_comms
@@ -129,7 +129,8 @@ def test_slab_hierarchy_and_smoother(oracle_mod, grid, levels, world):
     run_ranks(world, body)
 
 
-@pytest.mark.parametrize("grid,levels,world", [([32, 16, 16], 2, 2), ([32, 16, 16], 2, 4), ([48, 16, 16], 3, 3), ([64, 16, 16], 3, 8)])
+@pytest.mark.parametrize("grid,levels,world", [([32, 16, 16], 2, 2), ([32, 16, 16], 2, 4), ([48, 16, 16], 3, 3), ([64, 16, 16], 3, 8),
+                                               ([64, 32, 32], 3, 2), ([128, 16, 16], 2, 4)])   # the last two: 32 element layers per rank
 def test_slab_mg_pcg(oracle_mod, grid, levels, world):
     """MG-PCG (FMG preconditioner, 2 sweeps): fixed-iteration iterates and the converged solution against the oracle"""
     from ndr_b200.slab import ThreadHostSum, make_thread_comms
