@@ -24,6 +24,41 @@ __global__ void dfmaKernel(double *out, long long *cyc, int iters, double a, dou
     if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
 }
 
+// DFMA (ILP 8) interleaved with MIX independent integer / FP32 instructions per DFMA: does a DFMA hold the issue port for the 2
+// cycles its pipe needs (then time = 2 nDFMA + nOther), or can other instructions issue in its shadow (time = max)?
+template <int MIX>
+__global__ void mixKernel(double *out, long long *cyc, int iters, double a, double b, int ia, float fa) {
+    double x[8]; int n[8]; float f[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { x[i] = threadIdx.x * 1e-3 + i; n[i] = threadIdx.x + i; f[i] = threadIdx.x * 0.5f + i; }
+    __syncthreads();
+    long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                x[i] = fma(x[i], a, b);
+#pragma unroll
+                for (int m = 0; m < MIX; ++m) { if (m & 1) f[(i + m) & 7] = fmaf(f[(i + m) & 7], fa, 1.0f); else n[(i + m) & 7] = n[(i + m) & 7] * ia + 3; }
+            }
+    }
+    long long t1 = clock64();
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += x[i] + n[i] + f[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+    if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
+}
+template <int MIX>
+void runMix(int threads, double *out, long long *cyc) {
+    const int iters = 1000;
+    mixKernel<MIX><<<1, threads>>>(out, cyc, iters, 1.0000001, 1e-9, 3, 1.0001f);
+    cudaDeviceSynchronize();
+    long long h; cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost);
+    printf("MIX   warps/SM %2d  %d other instr per DFMA : %6.2f cycles per DFMA per warp\n", threads / 32, MIX, double(h) / (iters * 32.0));
+}
+
 __global__ void shflKernel(double *out, long long *cyc, int iters) {
     double x = threadIdx.x;
     long long t0 = clock64();
@@ -68,6 +103,7 @@ int main() {
     for (int threads : {32, 128, 256, 384, 512, 1024}) {
         runDfma<1>(threads, out, cyc); runDfma<2>(threads, out, cyc); runDfma<4>(threads, out, cyc); runDfma<8>(threads, out, cyc); runDfma<16>(threads, out, cyc);
     }
+    for (int threads : {128, 384}) { runMix<0>(threads, out, cyc); runMix<1>(threads, out, cyc); runMix<2>(threads, out, cyc); runMix<4>(threads, out, cyc); }
     for (int threads : {32, 128, 384}) {
         shflKernel<<<1, threads>>>(out, cyc, 2000); cudaDeviceSynchronize();
         long long h; cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost);
