@@ -185,4 +185,157 @@ gsFinePlaneKernel(Grid<3> g, K0Param<3> K, const Real *__restrict__ Ey, Real *u,
     }
 }
 
+// ---- assembled levels (l >= 1): the same plane-fused half sweep on the 27-point block stencil -------------------------
+// Replaces the cooperative all-colour kernel (gsStencilSweepKernel: 8 grid barriers per sweep, 2-3.3 TB/s).  A warp owns a
+// node: its 3 x 81 stencil coefficients stream from global memory (coalesced; two nodes per warp in flight), the 27
+// neighbour values come from the staged planes.  The staged box is zero-filled first: out-of-grid neighbours carry zero
+// coefficients (buildLevel1StencilKernel / galerkinStencilKernel) and must meet finite values.
+constexpr int kGsStPlaneThreads = 384;
+
+__global__ void __launch_bounds__(kGsStPlaneThreads, 1)
+gsStencilPlaneKernel(Grid<3> g, const Real *__restrict__ S, Real *u, const Real *__restrict__ b, const uint8_t *__restrict__ dmask, int px,
+                     int forward, int h, int rows, int RP) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cl = cg::this_cluster();
+    extern __shared__ __align__(16) unsigned char gsPlaneRaw[];
+    Real *raw = reinterpret_cast<Real *>(gsPlaneRaw), *box = raw + kGsPlanePad;
+    __shared__ __align__(8) unsigned long long bar;
+    constexpr int ROW = 81, J = 3;
+
+    const int nx = g.n[0], ny = g.n[1], nz = g.n[2];
+    const int CY = int(cl.num_blocks()), r = int(cl.block_rank());
+    const int slot = blockIdx.x / CY;
+    const int x = colourFirstPlane<3>(g, px << 2) + 2 * slot;
+    const int yOwn0 = r * h, yOwn1 = min((r + 1) * h, ny) - 1;
+    const int yLo = yOwn0 - 1;
+    const long long baseOdd = (long long)(reinterpret_cast<size_t>(u) >> 3) & 1;
+    const int planeSz = rows * RP;
+
+    { // zero the box (generic proxy), then hand it to the async proxy
+        double2 *z2 = reinterpret_cast<double2 *>(raw);
+        const int n2 = (3 * planeSz + kGsPlanePad) / 2;
+        for (int i = threadIdx.x; i < n2; i += kGsStPlaneThreads) z2[i] = make_double2(0.0, 0.0);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (threadIdx.x == 0) mbarInit(&bar, 32);
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        unsigned bytes = 0;
+        const long long total = (long long)g.nn * 24, ubase = (long long)reinterpret_cast<size_t>(u);
+        for (int q = threadIdx.x; q < 3 * rows; q += 32) {
+            const int pl = q / rows, lr = q - pl * rows;
+            const int xx = x + pl - 1, yy = yLo + lr;
+            if (xx < 0 || xx >= nx || yy < 0 || yy >= ny || yy > yOwn1 + 1 || yOwn0 > yOwn1) continue;
+            const long long row0 = ((long long)xx * ny + yy) * nz;
+            long long src = row0 * 24;
+            const int delta = int((ubase + src) & 8);
+            Real *dst = box + size_t(pl) * planeSz + size_t(lr) * RP + 2;
+            int need = nz * 24 + delta;
+            src -= delta;
+            if (src < 0) { dst[1] = u[0]; src += 16; dst += 2; need -= 16; }       // never read in front of the field: its first double by hand
+            int size = (need + 15) & ~15;
+            if (src + size > total) {                                              // ... nor behind it
+                size = need & ~15;
+                for (int i = size >> 3; i < (need >> 3); ++i) dst[i] = reinterpret_cast<const Real *>(reinterpret_cast<const char *>(u) + src)[i];
+            }
+            if (size > 0) { bulkLoad(dst, reinterpret_cast<const char *>(u) + src, unsigned(size), &bar); bytes += unsigned(size); }
+        }
+        mbarArriveExpectTx(&bar, bytes);
+    }
+    cl.sync();
+    mbarWait(&bar, 0);
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = kGsStPlaneThreads / 32;
+    const int fxp = (ny * nz) & 1, fyp = nz & 1;
+    int soff[J], sflip[J]; bool valid[J];
+#pragma unroll
+    for (int j = 0; j < J; ++j) { // entry e = lane + 32 j of a stencil row multiplies u[n + delta(e / 3)][e % 3]
+        const int e = lane + 32 * j;
+        valid[j] = e < ROW;
+        const int k = valid[j] ? e / 3 : 13, bc = valid[j] ? e % 3 : 0;
+        const int dx = k / 9 - 1, dy = (k / 3) % 3 - 1, dz = k % 3 - 1;
+        soff[j] = dx * planeSz + dy * RP + 3 * dz + bc;   // relative to the node itself in the staged centre plane
+        sflip[j] = (dx != 0 ? fxp : 0) ^ (dy != 0 ? fyp : 0);
+    }
+    struct Slot { Real Sv[3][J], uv[J], bv; unsigned mask; int n, own, p0, y, z; bool on; };
+    for (int ci = 0; ci < 4; ++ci) {
+        const int cyz = forward ? ci : 3 - ci;
+        const int py = (cyz >> 1) & 1, pz = cyz & 1;
+        const int yFirst = yOwn0 + ((yOwn0 ^ py) & 1);
+        const int cntY = yFirst <= yOwn1 ? (yOwn1 - yFirst) / 2 + 1 : 0, cntZ = (nz - 1 - pz) / 2 + 1, cnt = cntY * cntZ;
+        auto load = [&](int t, Slot &L) {
+            L.on = t < cnt;
+            if (!L.on) return;
+            const int iy = t / cntZ, iz = t - iy * cntZ;
+            L.y = yFirst + 2 * iy; L.z = pz + 2 * iz;
+            L.n = (x * ny + L.y) * nz + L.z;
+            L.p0 = int((baseOdd + ((long long)x * ny + L.y) * nz) & 1);
+            L.own = planeSz + (L.y - yLo) * RP + 2 + 3 * L.z;          // + p0: this node in the staged centre plane
+            const Real *Sn = S + size_t(L.n) * 3 * ROW + lane;
+#pragma unroll
+            for (int j = 0; j < J; ++j) {
+                L.uv[j] = valid[j] ? box[L.own + soff[j] + (L.p0 ^ sflip[j])] : 0.0;
+#pragma unroll
+                for (int a = 0; a < 3; ++a) L.Sv[a][j] = valid[j] ? Sn[a * ROW + 32 * j] : 0.0;
+            }
+            L.bv = (lane < 3) ? b[size_t(L.n) * 3 + lane] : 0.0;
+            L.mask = (lane == 0) ? unsigned(dmask[L.n]) : 0u;
+        };
+        auto update = [&](const Slot &L) {
+            if (!L.on) return;
+            Real acc[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                Real s = 0.0;
+#pragma unroll
+                for (int j = 0; j < J; ++j)
+                    if (valid[j]) s = fma(L.Sv[a][j], L.uv[j], s);
+                acc[a] = s;
+            }
+#pragma unroll
+            for (int a = 0; a < 3; ++a)
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) acc[a] += __shfl_xor_sync(0xffffffffu, acc[a], o);
+            Real M[9], tt[3], uo[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a)
+#pragma unroll
+                for (int c = 0; c < 3; ++c) { constexpr int e0 = 13 * 3; const int e = e0 + c; M[a * 3 + c] = __shfl_sync(0xffffffffu, L.Sv[a][e / 32], e % 32); }
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                constexpr int e0 = 13 * 3; const int e = e0 + c;
+                tt[c] = __shfl_sync(0xffffffffu, L.bv, c) - acc[c];
+                uo[c] = __shfl_sync(0xffffffffu, L.uv[e / 32], e % 32);
+            }
+            if (lane == 0) {
+                Real du[3];
+                if (forward) gsNodeSubst<3, true>(tt, M, L.mask, du); else gsNodeSubst<3, false>(tt, M, L.mask, du);
+                const int o = L.own + L.p0;
+                Real *gup = (L.y == yOwn0 && r > 0) ? cl.map_shared_rank(box, r - 1) + planeSz + (h + 1) * RP + 2 + L.p0 + 3 * L.z : nullptr;
+                Real *gdn = (L.y == yOwn1 && r + 1 < CY && yOwn1 + 1 < ny) ? cl.map_shared_rank(box, r + 1) + planeSz + 2 + L.p0 + 3 * L.z : nullptr;
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const Real nv = uo[c] + du[c];
+                    u[size_t(L.n) * 3 + c] = nv;
+                    box[o + c] = nv;
+                    if (gup) gup[c] = nv;
+                    if (gdn) gdn[c] = nv;
+                }
+            }
+        };
+        // two nodes per warp in flight, the next pair's coefficients requested before the current pair is reduced
+        Slot A, B, A2, B2;
+        int t = warp;
+        load(t, A); load(t + nw, B);
+        while (t < cnt) {
+            const int tn = t + 2 * nw;
+            load(tn, A2); load(tn + nw, B2);
+            update(A); update(B);
+            A = A2; B = B2;
+            t = tn;
+        }
+        cl.sync();
+    }
+}
+
 } // namespace vfem
