@@ -63,12 +63,6 @@ gsFineTileKernel(Grid<3> g, K0Param<3> K, const Real *__restrict__ Ey, Real *u, 
     const int zLo = z0 - 1, BZ = 2 * tzc + 1;            // node window [zLo, zLo + BZ) of every staged row
 
     const long long baseOdd = (long long)(reinterpret_cast<size_t>(u) >> 3) & 1;
-    { // the box starts as zeros (generic proxy), then goes to the async proxy: out-of-grid neighbours - whole rows and the z = -1 /
-      // z = nz slots - are read as 0.0 without any per-value test (their elements carry modulus 0, but 0 * garbage could be NaN)
-        double2 *z2 = reinterpret_cast<double2 *>(box);
-        for (int i = threadIdx.x; i < BX * BY * RP / 2; i += Cfg::NT) z2[i] = make_double2(0.0, 0.0);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    }
     if (threadIdx.x == 0) mbarInit(&bar, 32);
     __syncthreads();
     if (threadIdx.x < 32) { // warp 0 stages the rows; every lane arrives once with the bytes of the copies it issued
@@ -81,20 +75,19 @@ gsFineTileKernel(Grid<3> g, K0Param<3> K, const Real *__restrict__ Ey, Real *u, 
             const int x = x0 - 1 + bx, y = y0 - 1 + by;
             if (x < 0 || x >= nx || y < 0 || y >= ny) continue;
             const long long row0 = ((long long)x * ny + y) * nz;
-            long long src = (row0 + za) * 24;
+            const long long src = (row0 + za) * 24;
             const int delta = int((ubase + src) & 8);               // u itself may be only 8-byte aligned (a view into a larger field)
             const int orow = 2 + int((baseOdd + row0 + z0 + 1) & 1); // rowParity: see the readers below
             Real *dst = box + r * RP + orow + 3 * (za - zLo) - (delta >> 3);
-            int need = (zb - za) * 24 + delta;
-            src -= delta;
-            if (src < 0) { dst[1] = u[0]; src += 16; dst += 2; need -= 16; }   // never read in front of the field: its first double by hand
+            const int need = (zb - za) * 24 + delta;
             int size = (need + 15) & ~15;
-            if (src + size > total) { // ... nor behind it: the last double by hand
+            if (src - delta + size > total) { // the array ends inside the last 16-byte chunk: copy that double by hand
                 size = need & ~15;
-                for (int i = size >> 3; i < (need >> 3); ++i) dst[i] = reinterpret_cast<const Real *>(reinterpret_cast<const char *>(u) + src)[i];
+                const int first = size >> 3; // doubles covered by the bulk copy
+                for (int i = first; i < (need >> 3); ++i) dst[i] = reinterpret_cast<const Real *>(reinterpret_cast<const char *>(u) + src - delta)[i];
             }
             if (size > 0) {
-                bulkLoad(dst, reinterpret_cast<const char *>(u) + src, unsigned(size), &bar);
+                bulkLoad(dst, reinterpret_cast<const char *>(u) + src - delta, unsigned(size), &bar);
                 bytes += unsigned(size);
             }
         }
@@ -152,12 +145,14 @@ gsFineTileKernel(Grid<3> g, K0Param<3> K, const Real *__restrict__ Ey, Real *u, 
             for (int i = 0; i < 4; ++i) { const double2 t2 = *reinterpret_cast<const double2 *>(row + 2 * i); w[2 * i] = t2.x; w[2 * i + 1] = t2.y; }
             w[8] = row[8];
         }
+        const bool okr = (x + dx >= 0) && (x + dx < nx) && (y + dy >= 0) && (y + dy < ny);
 #pragma unroll
         for (int dzi = 0; dzi < 3; ++dzi) {
             const int dz = dzi - 1, k = r * 3 + dzi;
+            const bool ok = okr && (z + dz >= 0) && (z + dz < nz);
             Real v[3];
 #pragma unroll
-            for (int c = 0; c < 3; ++c) v[c] = w[dzi * 3 + c];
+            for (int c = 0; c < 3; ++c) v[c] = ok ? w[dzi * 3 + c] : 0.0;
             if (k == 13) { uc[0] = v[0]; uc[1] = v[1]; uc[2] = v[2]; }
 #pragma unroll
             for (int s = 0; s < 8; ++s) { // incident element s holds this node at offset sd - 1 + qd = dd  =>  qd = dd + 1 - sd in {0, 1}

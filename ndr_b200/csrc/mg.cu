@@ -3,7 +3,6 @@
 #include "kernels.cuh"
 #include "kernels_mg.cuh"
 #include "gs_tile.cuh"
-#include "gs_plane.cuh"
 #include "block_tri.h"
 
 namespace vfem {
@@ -26,7 +25,6 @@ MG<N>::MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels, std::shared_
     useGraphs = getenv("VFEM_NO_GRAPH") == nullptr && (!slab() || comm->graphSafe());
     if (const char *v = getenv("VFEM_GS_VARIANT")) gsVariant = atoi(v);
     fusedSweeps = getenv("VFEM_NO_FUSED_SWEEPS") == nullptr;
-    if (const char *v = getenv("VFEM_STENCIL_PLANE")) stencilPlane = atoi(v) != 0;
     int E[N];
     for (int d = 0; d < N; ++d) E[d] = fine->g.E[d];
     lv.resize(numCoarseningLevels + 1);
@@ -314,58 +312,6 @@ static inline bool launchGsFineTile(const Grid<3> &g, const K0Param<3> &K, const
 }
 static inline bool launchGsFineTile(const Grid<2> &, const K0Param<2> &, const Real *, Real *, const Real *, const uint8_t *, int, int, cudaStream_t, int) { return false; }
 
-// 3-D fine level, plane-fused form (gs_plane.cuh): one launch per HALF sweep (the four colours of the even / odd node planes)
-static inline bool launchGsFinePlane(const Grid<3> &g, const K0Param<3> &K, const Real *Ey, Real *u, const Real *b, const uint8_t *dmask, int px,
-                                     int forward, cudaStream_t stream) {
-    if (reinterpret_cast<size_t>(u) & 7) return false;
-    static const int forceCy = getenv("VFEM_GS_PLANE_CY") ? atoi(getenv("VFEM_GS_PLANE_CY")) : 0;
-    const GsPlanePlan p = planGsPlane(g, forceCy);
-    if (p.cy == 0) return false;
-    const int planes = colourPlaneCount<3>(g, px << 2);
-    if (planes <= 0) return true;
-    static bool once = (cudaFuncSetAttribute(gsFinePlaneKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kGsPlaneSmemMax)), true);
-    (void)once;
-    cudaLaunchConfig_t cfg = {};
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = unsigned(p.cy); attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.gridDim = dim3(unsigned(p.cy * planes)); cfg.blockDim = dim3(kGsPlaneThreads); cfg.dynamicSmemBytes = p.smem; cfg.stream = stream;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    VFEM_CUDA(cudaLaunchKernelEx(&cfg, gsFinePlaneKernel, g, K, Ey, u, b, dmask, px, forward, p.h, p.rows, p.pitch));
-    return true;
-}
-// assembled levels, plane-fused half sweep (gsStencilPlaneKernel)
-static inline bool launchGsStencilPlane(const Grid<3> &g, const Real *S, Real *u, const Real *b, const uint8_t *dmask, int px, int forward,
-                                        cudaStream_t stream) {
-    if (reinterpret_cast<size_t>(u) & 7) return false;
-    static const int forceCy = getenv("VFEM_GS_STPLANE_CY") ? atoi(getenv("VFEM_GS_STPLANE_CY")) : 0;
-    GsPlanePlan p = planGsPlane(g, forceCy);
-    if (!forceCy) { // streaming-bound: as many CTAs as the planes allow (strips of >= 3 rows), up to the device width
-        const int planesHalf = std::max(1, (g.n[0] + 1) / 2);
-        for (int cy : {8, 4, 2, 1}) {
-            if (cy * planesHalf > 296 && cy > 1) continue;
-            if ((g.n[1] + cy - 1) / cy < 3 && cy > 1) continue;
-            const GsPlanePlan q = planGsPlane(g, cy);
-            if (q.cy) { p = q; break; }
-        }
-    }
-    if (p.cy == 0) return false;
-    const int planes = colourPlaneCount<3>(g, px << 2);
-    if (planes <= 0) return true;
-    static bool once = (cudaFuncSetAttribute(gsStencilPlaneKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kGsPlaneSmemMax)), true);
-    (void)once;
-    cudaLaunchConfig_t cfg = {};
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = unsigned(p.cy); attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.gridDim = dim3(unsigned(p.cy * planes)); cfg.blockDim = dim3(kGsStPlaneThreads); cfg.dynamicSmemBytes = p.smem; cfg.stream = stream;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    VFEM_CUDA(cudaLaunchKernelEx(&cfg, gsStencilPlaneKernel, g, S, u, b, dmask, px, forward, p.h, p.rows, p.pitch));
-    return true;
-}
-static inline bool launchGsStencilPlane(const Grid<2> &, const Real *, Real *, const Real *, const uint8_t *, int, int, cudaStream_t) { return false; }
-static inline bool launchGsFinePlane(const Grid<2> &, const K0Param<2> &, const Real *, Real *, const Real *, const uint8_t *, int, int, cudaStream_t) { return false; }
-
 // Halo traffic of a coloured sweep (slab mode): the colours whose axis-0 parity is even (the first half of the forward
 // order, MG.hh:292-294) only read odd ghost planes and vice versa, and own0 is even / own1 odd on interior faces, so a
 // sweep needs ONE one-directional plane shift after each half: even half -> first owned plane goes down, odd half ->
@@ -374,23 +320,13 @@ template <int N>
 void MG<N>::smoothColoured(size_t l, Real *u, const Real *b, bool forward) {
     const Level &L = lv.at(l);
     const Real *Ey = (l == 0) ? sim->moduli() : nullptr;
-    if (l == 0 && N == 3 && gsVariant == 5) { // plane-fused: the even-plane colours, then the odd-plane colours (reversed for a backward sweep)
-        bool ok = true;
-        for (int half = 0; half < 2 && ok; ++half) {
-            const int px = forward ? half : 1 - half;
-            ok = launchGsFinePlane(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), px, forward ? 1 : 0, stream);
-            if (ok) { countLaunch(); if (slab()) exchange(l, u, px ? XUP : XDOWN); }
-            else if (half == 1) throw std::runtime_error("plane-fused Gauss-Seidel: second half could not be launched");
-        }
-        if (ok) return;
-    }
     for (int i = 0; i < NPE; ++i) {
         const int colour = forward ? i : NPE - 1 - i; // MG.hh:318-320
         const int cnt = colourCount<N>(L.g, colour);
         if (cnt > 0) {
             const unsigned blocks = unsigned((cnt + kBlock - 1) / kBlock);
             if (l == 0) { // gsVariant 0: one thread per node gathering from global memory (the 2-D path and the fallback)
-                if (!(N == 3 && gsVariant != 0 && launchGsFineTile(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0, stream, gsVariant)))
+                if (!(N == 3 && gsVariant != 0 && launchGsFineTile(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0, stream, gsVariant == 1 && cnt < 60000 ? 3 : gsVariant)))
                     gsFineKernel<N, 4><<<blocks, kBlock, 0, stream>>>(L.g, sim->K0, Ey, u, b, maskOf(*this, 0), colour, forward ? 1 : 0);
             }
             else gsStencilWarpKernel<N><<<warpGridBlocks(cnt), kWarpBlock, 0, stream>>>(L.g, L.S.p, u, b, maskOf(*this, l), colour, forward ? 1 : 0, cnt);
@@ -413,17 +349,6 @@ template <int N>
 void MG<N>::smooth(size_t l, Real *u, const Real *b, bool forward, size_t sweeps) {
     if (l == 0 || !fusedSweeps || sweeps == 0) { for (size_t i = 0; i < sweeps; ++i) smoothColoured(l, u, b, forward); return; }
     const Level &L = lv.at(l);
-    if (N == 3 && stencilPlane) { // plane-fused half sweeps (gs_plane.cuh): even planes, then odd planes (reversed for a backward sweep)
-        bool ok = true;
-        for (size_t i = 0; i < sweeps && ok; ++i)
-            for (int half = 0; half < 2 && ok; ++half) {
-                const int px = forward ? half : 1 - half;
-                ok = launchGsStencilPlane(L.g, L.S.p, u, b, maskOf(*this, l), px, forward ? 1 : 0, stream);
-                if (ok) { countLaunch(); if (slab()) exchange(l, u, px ? XUP : XDOWN); }
-                else if (i > 0 || half > 0) throw std::runtime_error("plane-fused stencil Gauss-Seidel: launch failed mid-sweep");
-            }
-        if (ok) return;
-    }
     if (sweepGridBlocks == 0) {
         int dev = 0, sms = 148, per = 1;
         VFEM_CUDA(cudaGetDevice(&dev));

@@ -58,8 +58,7 @@ struct MG : MGBase {
         }
     };
     bool useGraphs = true, fusedSweeps = true;
-    bool stencilPlane = false;      // levels >= 1: plane-fused half-sweep kernel (gs_plane.cuh) instead of the cooperative all-colour kernel
-    int gsVariant = 1;              // fine-level GS, 3-D: 1 = shared-memory tile kernel (gs_tile.cuh), 0 = per-node gather from global memory
+    int gsVariant = 1;              // fine-level GS, 3-D: 1 = shared-memory tile kernel (gs_tile.cuh; 2 x 4 site tiles below 60 k nodes per colour, 2 x 2 above), 2..4 = forced tile shape, 0 = per-node gather from global memory
     cudaStream_t captureStream = nullptr;
     cudaGraphExec_t pgExec = nullptr;
     PrecondKey pgKey;
