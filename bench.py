@@ -286,7 +286,10 @@ def roofline_block(wl, kms, hbm_peak, peak_src):
 
 def kernel_source_sha():
     import hashlib
-    return hashlib.sha256(open(os.path.join(ROOT, "ndr_b200", "csrc", "apply_march.cuh"), "rb").read()).hexdigest()[:16]
+    h = hashlib.sha256()
+    for f in ("apply_march.cuh", "apply_march_tma.cuh"):
+        h.update(open(os.path.join(ROOT, "ndr_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
 
 
 def _lib_check(rc):
