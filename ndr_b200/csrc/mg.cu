@@ -132,6 +132,7 @@ MG<N>::~MG() {
     if (pgExec) cudaGraphExecDestroy(pgExec);
     if (captureStream) cudaStreamDestroy(captureStream);
     if (h_scal) cudaFreeHost(h_scal);
+    for (auto &kv : haloGraphs) if (kv.second) cudaGraphExecDestroy(kv.second);
     if (haloStream) cudaStreamDestroy(haloStream);
     if (haloFork) cudaEventDestroy(haloFork);
     if (haloJoin) cudaEventDestroy(haloJoin);
@@ -254,14 +255,54 @@ template <int N>
 template <int MODE>
 void MG<N>::exchangeApplyFine(Real *u, const Real *b, Real *out) {
     const Grid<N> &g = lv[0].g;
-    const int o0 = g.own0, o1 = g.own1, E0 = g.E[0];
-    const bool below = o0 > 0, above = o1 + 1 < g.n[0];
+    const int o0 = g.own0, o1 = g.own1;
     if (!slab() || o1 - o0 < 3 || getenv("VFEM_NO_HALO_OVERLAP")) {
         exchange(0, u, XUP | XDOWN);
         applyMode<MODE>(0, u, b, out);
         return;
     }
     sim->moduli(); // a stale E(rho) is refreshed on the solver stream BEFORE the fork
+    syncMasks();
+    // The overlapped form is 1 NCCL group + 3 kernel launches + 4 event operations on two streams: launch-bound next to a
+    // 20 us kernel.  Its SECOND call with the same arrays captures it into a CUDA graph (fork / join included), later calls replay it.
+    if (useGraphs && comm->graphSafe() && comm->sideStreamSafe() && !getenv("VFEM_NO_HALO_GRAPH")) {
+        HaloGraphKey key{u, b, out, MODE, sim->k0Version, sim->applyVariant};
+        auto it = haloGraphs.find(key);
+        if (it == haloGraphs.end()) {
+            if (haloGraphs.size() >= 64) { for (auto &kv : haloGraphs) if (kv.second) cudaGraphExecDestroy(kv.second); haloGraphs.clear(); }
+            haloGraphs.emplace(key, nullptr);   // first call: run it plainly (also sets function attributes, plans the views)
+        } else {
+            if (!it->second) {
+                if (!captureStream) VFEM_CUDA(cudaStreamCreateWithFlags(&captureStream, cudaStreamNonBlocking));
+                VFEM_CUDA(cudaStreamSynchronize(stream));
+                const cudaStream_t saved = stream, savedSim = sim->stream;
+                const unsigned long long before = g_launchCount;
+                stream = captureStream; sim->stream = captureStream;
+                cudaGraph_t graph = nullptr;
+                VFEM_CUDA(cudaStreamBeginCapture(captureStream, cudaStreamCaptureModeRelaxed));
+                try { exchangeApplyFineBody<MODE>(u, b, out); }
+                catch (...) { cudaStreamEndCapture(captureStream, &graph); if (graph) cudaGraphDestroy(graph); stream = saved; sim->stream = savedSim; throw; }
+                stream = saved; sim->stream = savedSim;
+                VFEM_CUDA(cudaStreamEndCapture(captureStream, &graph));
+                haloGraphLaunches = g_launchCount - before;
+                g_launchCount = before;
+                VFEM_CUDA(cudaGraphInstantiate(&it->second, graph, 0));
+                cudaGraphDestroy(graph);
+            }
+            VFEM_CUDA(cudaGraphLaunch(it->second, stream));
+            countLaunch(haloGraphLaunches);
+            return;
+        }
+    }
+    exchangeApplyFineBody<MODE>(u, b, out);
+}
+
+template <int N>
+template <int MODE>
+void MG<N>::exchangeApplyFineBody(Real *u, const Real *b, Real *out) {
+    const Grid<N> &g = lv[0].g;
+    const int o0 = g.own0, o1 = g.own1, E0 = g.E[0];
+    const bool below = o0 > 0, above = o1 + 1 < g.n[0];
     cudaStream_t hs = stream;
     if (comm->sideStreamSafe()) {
         if (!haloStream) {

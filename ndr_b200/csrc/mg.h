@@ -13,6 +13,8 @@
 #include "kernels_vec.cuh"
 #include "comm.h"
 #include <functional>
+#include <map>
+#include <tuple>
 
 namespace vfem {
 
@@ -90,6 +92,15 @@ struct MG : MGBase {
     void exchange(size_t l, Real *v, int dirs);                 // halo planes of a level-l vector
     // fine level: refresh the ghost planes of u AND apply the operator, the shift hidden behind the interior layers
     template <int MODE> void exchangeApplyFine(Real *u, const Real *b, Real *out);
+    template <int MODE> void exchangeApplyFineBody(Real *u, const Real *b, Real *out);
+    struct HaloGraphKey {
+        const Real *u, *b, *out; int mode; unsigned long long k0Version; int applyVariant;
+        bool operator<(const HaloGraphKey &o) const {
+            return std::tie(u, b, out, mode, k0Version, applyVariant) < std::tie(o.u, o.b, o.out, o.mode, o.k0Version, o.applyVariant);
+        }
+    };
+    std::map<HaloGraphKey, cudaGraphExec_t> haloGraphs;   // captured halo-shift + apply, per array triple
+    unsigned long long haloGraphLaunches = 0;
     void exchangeHostMask(size_t l);
     void allreduce(Real *devScalars, size_t n) { if (slab()) comm->allreduceSum(devScalars, n, stream); }
     size_t ownedOffset(size_t l) const { return size_t(lv[l].g.own0) * lv[l].g.ninc[0] * N; }
