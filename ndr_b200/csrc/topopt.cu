@@ -9,13 +9,18 @@ struct Dims { int nd; int E[3]; };
 
 // ---- SmoothingFilter (Filter.hh:105-162): row i has weight 1/k_i on every in-grid voxel of the cube
 // |delta_d| <= r (NDVector.hh:235-262).  BACKPROP applies the transposed matrix. ------------------------
+// Slab form: D holds the GLOBAL dimensions (the clipping of the box and the counts are those of the undecomposed grid); `in`
+// starts at global layer inLo of axis 0 and must hold every in-grid layer within r of the outputs, `out` starts at global layer
+// outLo and has n entries.  The undecomposed call is inLo = outLo = 0, n = all elements.
 template <bool BACKPROP>
-__global__ void __launch_bounds__(kRedBlock) smoothingKernel(Dims D, int r, const Real *__restrict__ in, Real *__restrict__ out, size_t n) {
+__global__ void __launch_bounds__(kRedBlock) smoothingKernel(Dims D, int r, const Real *__restrict__ in, Real *__restrict__ out, size_t n,
+                                                             int inLo, int outLo) {
     size_t i = size_t(blockIdx.x) * kRedBlock + threadIdx.x;
     if (i >= n) return;
     // grids with fewer than 3 axes are padded with trailing unit axes (the clipped box is then 1 wide there)
     int c[3], E[3] = {D.E[0], D.E[1], D.E[2]};
-    { size_t t = i; for (int d = 2; d >= 0; --d) { c[d] = int(t % size_t(E[d])); t /= size_t(E[d]); } }
+    { size_t t = i; for (int d = 2; d > 0; --d) { c[d] = int(t % size_t(E[d])); t /= size_t(E[d]); } c[0] = int(t) + outLo; }
+    in -= size_t(inLo) * E[1] * E[2];
     const int rr[3] = {r, r, r};
     int lo[3], hi[3];
     for (int d = 0; d < 3; ++d) { lo[d] = max(c[d] - rr[d], 0); hi[d] = min(c[d] + rr[d], E[d] - 1); }
@@ -82,11 +87,11 @@ __global__ void __launch_bounds__(kRedBlock) diffSqKernel(const Real *__restrict
 static inline unsigned eblocks(size_t n) { return unsigned((n + kRedBlock - 1) / kRedBlock); }
 
 static void launchFilter(const Dims &D, const FilterDesc &f, bool backprop, const Real *in, const Real *vars, Real *out, size_t n,
-                         cudaStream_t stream, std::vector<Real> *hA, std::vector<Real> *hB, std::vector<Real> *hC) {
+                         cudaStream_t stream, std::vector<Real> *hA, std::vector<Real> *hB, std::vector<Real> *hC, int inLo = 0, int outLo = 0) {
     if (f.type == FILTER_SMOOTHING) {
         const int r = int(size_t(f.param));
-        if (backprop) smoothingKernel<true><<<eblocks(n), kRedBlock, 0, stream>>>(D, r, in, out, n);
-        else smoothingKernel<false><<<eblocks(n), kRedBlock, 0, stream>>>(D, r, in, out, n);
+        if (backprop) smoothingKernel<true><<<eblocks(n), kRedBlock, 0, stream>>>(D, r, in, out, n, inLo, outLo);
+        else smoothingKernel<false><<<eblocks(n), kRedBlock, 0, stream>>>(D, r, in, out, n, inLo, outLo);
         VFEM_CHECK_LAUNCH(); countLaunch();
     } else if (f.type == FILTER_PROJECTION) {
         if (backprop) projectionBackpropKernel<<<eblocks(n), kRedBlock, 0, stream>>>(f.param, in, vars, out, n);

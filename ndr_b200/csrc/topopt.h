@@ -51,10 +51,27 @@ struct Problem : ProblemBase {
     Real lambdaMin = 1.0, lambdaMax = 2.0, lastLambda = 0.0; int lastBisections = 0;
     std::vector<Real> hostA, hostB, hostC;   // staging for callback filters
 
+    // Slab decomposition ("rho/E ghost element layer"): the variables of a rank are its LOCAL element layers - `ghost`
+    // layers below that mirror the lower neighbour's top layers, then the owned ones.  Pointwise passes run on all of them
+    // (consistent in -> consistent out); the box filter fetches `radius` layers from the rank above into the tail every buffer
+    // carries, computes the owned layers with the GLOBAL clipping, and refreshes the ghost layers from the owner; reductions
+    // run over the owned layers + one all-reduce.  Single device: ghost = 0, no tail, no exchange.
+    bool slab() const { return obj->mg && obj->mg->slab(); }
+    size_t planeElems() const { size_t p = 1; for (int d = 1; d < N; ++d) p *= size_t(sim->g.E[d]); return p; }
+    int ghostLayers() const { return slab() ? obj->mg->lv[0].g.own0 : 0; }
+    int ghostSpan() const { return slab() ? 1 << (int(obj->mg->numLevels()) - 1) : 0; }     // layers a rank mirrors from below (ranks > 0)
+    size_t ownedOffset() const { return size_t(ghostLayers()) * planeElems(); }
+    size_t ownedCount() const { return numVars() - ownedOffset(); }
+    size_t globalVars() const { return size_t(sim->globalE0) * planeElems(); }
+    void refreshGhostBelow(Real *v);            // ghost layers <- the lower neighbour's top owned layers
+    void fetchAbove(Real *v, int layers);       // tail of v <- the upper neighbour's first owned layers
+    Real reduceOwned(int slot);                 // all-reduce + read back of a per-rank partial sum
+
     Problem(std::shared_ptr<Sim<N>> s, std::shared_ptr<Objective<N>> o, const std::vector<Real> &volFracs, const std::vector<FilterDesc> &fl);
     size_t numVars() const { return sim->numElements(); }
     void applyFilter(const FilterDesc &f, const Real *in, Real *out);
     void backpropFilter(const FilterDesc &f, const Real *in, const Real *vars, Real *out);
+    void slabSmoothing(const FilterDesc &f, bool backprop, Real *in, Real *out);
     bool setVars(const Real *x, MemSpace ms, bool forceUpdate);          // Problem.hh:42-65
     Real evaluateObjective();                                            // Problem.hh:88-94
     void evaluateObjectiveGradient(Real *gradDev);                       // Problem.hh:98-113

@@ -50,18 +50,55 @@ Problem<N>::Problem(std::shared_ptr<Sim<N>> s, std::shared_ptr<Objective<N>> o, 
     : sim(s), obj(o), volumeFractions(volFracs), filters(fl) {
     dim = N;
     const size_t ne = sim->numElements();
+    const size_t tail = size_t(ghostSpan()) * planeElems(); // room for the layers fetched from the rank above (radius <= ghost span)
     cached.resize(filters.size() + 1);
-    for (auto &c : cached) { c.alloc(ne); c.zero(sim->stream); }
-    s0.alloc(ne); s1.alloc(ne); s2.alloc(ne); s3.alloc(ne);
+    for (auto &c : cached) { c.alloc(ne + tail); c.zero(sim->stream); }
+    s0.alloc(ne + tail); s1.alloc(ne + tail); s2.alloc(ne + tail); s3.alloc(ne + tail);
+    if (slab())
+        for (const FilterDesc &f : filters)
+            if (f.type == FILTER_CALLBACK) throw std::runtime_error("callback filters are not available on a slab-decomposed problem");
+}
+
+template <int N>
+void Problem<N>::refreshGhostBelow(Real *v) {
+    if (!slab()) return;
+    const size_t cnt = size_t(ghostSpan()) * planeElems();
+    obj->mg->comm->shift(v + numVars() - cnt, v, v, v, cnt, true, false, sim->stream);
+}
+template <int N>
+void Problem<N>::fetchAbove(Real *v, int layers) {
+    if (!slab() || layers <= 0) return;
+    const size_t cnt = size_t(layers) * planeElems();
+    obj->mg->comm->shift(v, v, v + ownedOffset(), v + numVars(), cnt, false, true, sim->stream);
+}
+template <int N>
+Real Problem<N>::reduceOwned(int slot) {
+    Reducer &red = obj->red;
+    if (slab()) obj->mg->comm->allreduceSum(red.scal.p + slot, 1, sim->stream);
+    return red.fetch(slot, sim->stream);
 }
 
 template <int N>
 void Problem<N>::applyFilter(const FilterDesc &f, const Real *in, Real *out) {
+    if (slab() && f.type == FILTER_SMOOTHING) { slabSmoothing(f, false, const_cast<Real *>(in), out); return; }
     launchFilter(dimsOf(*sim), f, false, in, nullptr, out, numVars(), sim->stream, &hostA, &hostB, &hostC);
 }
 template <int N>
 void Problem<N>::backpropFilter(const FilterDesc &f, const Real *in, const Real *vars, Real *out) {
+    if (slab() && f.type == FILTER_SMOOTHING) { slabSmoothing(f, true, const_cast<Real *>(in), out); return; }
     launchFilter(dimsOf(*sim), f, true, in, vars, out, numVars(), sim->stream, &hostA, &hostB, &hostC);
+}
+// box filter (or its transpose) on a slab: `in` is one of the problem's own buffers (consistent ghost layers, room for the tail)
+template <int N>
+void Problem<N>::slabSmoothing(const FilterDesc &f, bool backprop, Real *in, Real *out) {
+    const int r = int(size_t(f.param));
+    if (r > ghostSpan()) throw std::runtime_error("slab-decomposed smoothing filter: the radius must not exceed 2^numCoarseningLevels element layers");
+    fetchAbove(in, r);
+    Dims D = dimsOf(*sim);
+    D.E[0] = sim->globalE0;
+    launchFilter(D, f, backprop, in, nullptr, out + ownedOffset(), ownedCount(), sim->stream, &hostA, &hostB, &hostC, sim->layerLo,
+                 sim->layerLo + ghostLayers());
+    refreshGhostBelow(out);
 }
 
 template <int N>
@@ -74,11 +111,12 @@ bool Problem<N>::setVars(const Real *x, MemSpace ms, bool forceUpdate) {
         xd = s0.p;
     }
     if (!forceUpdate && varsAreSet) { // Problem.hh:50-51
-        diffSqKernel<<<reduceBlocks(ne), kRedBlock, 0, sim->stream>>>(xd, cached[0].p, ne, red.rw, red.scal.p + 6);
+        diffSqKernel<<<reduceBlocks(ownedCount()), kRedBlock, 0, sim->stream>>>(xd + ownedOffset(), cached[0].p + ownedOffset(), ownedCount(), red.rw, red.scal.p + 6);
         VFEM_CHECK_LAUNCH(); countLaunch();
-        if (std::sqrt(red.fetch(6, sim->stream)) < 1e-16) return false;
+        if (std::sqrt(reduceOwned(6)) < 1e-16) return false;
     }
     if (xd != cached[0].p) VFEM_CUDA(cudaMemcpyAsync(cached[0].p, xd, ne * sizeof(Real), cudaMemcpyDeviceToDevice, sim->stream));
+    refreshGhostBelow(cached[0].p); // the caller's ghost layers are not trusted
     for (size_t i = 0; i < filters.size(); ++i) applyFilter(filters[i], cached[i].p, cached[i + 1].p);
     obj->updateCache(cached.back().p);
     varsAreSet = true;
@@ -95,21 +133,23 @@ template <int N>
 void Problem<N>::evaluateObjectiveGradient(Real *gradDev) {
     if (!varsAreSet) throw std::runtime_error("Must call setVars first!");
     const size_t nf = filters.size();
-    Real *cur = (nf % 2 == 0) ? gradDev : s3.p, *other = (nf % 2 == 0) ? s3.p : gradDev;
+    Real *cur = s2.p, *other = s3.p; // the problem's own buffers: a slab filter needs their tail
     obj->gradient(cur);
+    refreshGhostBelow(cur); // ghost elements see stale displacement planes: their sensitivities come from the owner
     for (size_t i = 0; i < nf; ++i) { // reverse filter chain, each evaluated at its own input vars (Problem.hh:108-111)
         backpropFilter(filters[nf - 1 - i], cur, cached[nf - 1 - i].p, other);
         std::swap(cur, other);
     }
+    VFEM_CUDA(cudaMemcpyAsync(gradDev, cur, numVars() * sizeof(Real), cudaMemcpyDeviceToDevice, sim->stream));
 }
 
 template <int N>
 Real Problem<N>::meanOf(const Real *v) {
     Reducer &red = obj->red;
-    const size_t ne = numVars();
-    sumKernel<<<reduceBlocks(ne), kRedBlock, 0, sim->stream>>>(v, ne, red.rw, red.scal.p + 7);
+    const size_t ne = ownedCount();
+    sumKernel<<<reduceBlocks(ne), kRedBlock, 0, sim->stream>>>(v + ownedOffset(), ne, red.rw, red.scal.p + 7);
     VFEM_CHECK_LAUNCH(); countLaunch();
-    return red.fetch(7, sim->stream) / Real(ne);
+    return reduceOwned(7) / Real(slab() ? globalVars() : ne);
 }
 
 template <int N>
@@ -122,13 +162,14 @@ template <int N>
 void Problem<N>::evaluateConstraintJacobianRow(size_t ci, Real *rowDev) {
     if (!varsAreSet) throw std::runtime_error("Must call setVars first!");
     const size_t nf = filters.size(), ne = numVars();
-    Real *cur = (nf % 2 == 0) ? rowDev : s3.p, *other = (nf % 2 == 0) ? s3.p : rowDev;
-    fillKernel<<<eblocks(ne), kRedBlock, 0, sim->stream>>>(cur, -1.0 / (volumeFractions.at(ci) * Real(ne)), ne); // Constraint.hh:29-31
+    Real *cur = s2.p, *other = s3.p;
+    fillKernel<<<eblocks(ne), kRedBlock, 0, sim->stream>>>(cur, -1.0 / (volumeFractions.at(ci) * Real(slab() ? globalVars() : ne)), ne); // Constraint.hh:29-31
     VFEM_CHECK_LAUNCH(); countLaunch();
     for (size_t i = 0; i < nf; ++i) {
         backpropFilter(filters[nf - 1 - i], cur, cached[nf - 1 - i].p, other);
         std::swap(cur, other);
     }
+    VFEM_CUDA(cudaMemcpyAsync(rowDev, cur, ne * sizeof(Real), cudaMemcpyDeviceToDevice, sim->stream));
 }
 
 // constraint value of the OC candidate x(lambda) after the full filter chain; leaves x(lambda) in xOut

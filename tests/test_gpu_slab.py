@@ -161,3 +161,50 @@ def test_slab_mg_pcg(oracle_mod, grid, levels, world):
         J = 0.5 * s.dot(fl, u)
         assert abs(J - 0.5 * float(np.sum(f * want[100][0]))) < 1e-10 * abs(J)
     run_ranks(world, body)
+
+
+@pytest.mark.parametrize("grid,levels,world", [([32, 16, 16], 2, 2), ([32, 16, 16], 2, 4), ([48, 16, 16], 3, 3)])
+def test_slab_topology_optimization_iteration(oracle_mod, grid, levels, world):
+    """The density pipeline on slabs (SURVEY 8e "rho/E ghost element layer"): box filter with a layer halo + global clipping,
+    projection, volume constraint (owned sums + all-reduce), objective / gradient chain and three optimality-criterion steps
+    against the oracle's undecomposed problem: lambda equal, max-abs density <= 1e-8 on the owned layers of every rank."""
+    import ndr_b200.pyVoxelFEM as V
+    from ndr_b200.slab import ThreadHostSum, make_thread_comms
+    vol = 0.4
+    o, _ = oracle_problem(oracle_mod, grid, levels)
+    x0g = np.random.default_rng(11).uniform(0.25, 0.6, o.ne)
+    o.set_densities(x0g)
+    o.top_create(True, vol, [("smoothing", 1), ("projection", 1.0)])
+    o.top_set_solver(100, 1e-11, 1, 2, True, False)
+    o.top_set_vars(x0g)
+    ref = {"dens": o.top_vars(-1).copy(), "J": o.top_objective(), "grad": o.top_gradient().copy(), "c": o.top_constraint(),
+           "jac": o.top_constraint_jac().copy(), "steps": []}
+    for _ in range(3):
+        lam, _ = o.oc_step()
+        ref["steps"].append((lam, o.top_vars(0).copy(), o.top_objective()))
+    comms, hs = make_thread_comms(world), ThreadHostSum(world)
+
+    def body(r):
+        s = make_rank(grid, levels, r, world, comms, hs, x0g)
+        L = s.layout
+        mg = s.multigrid()
+        obj = V.MultigridComplianceObjective(mg)
+        top = V.TopologyOptimizationProblem(s.tps, obj, [V.TotalVolumeConstraint(vol)], [V.SmoothingFilter(), V.ProjectionFilter()])
+        obj.tol = 1e-11
+        loc, own, gown = L.elem_slice(), L.owned_elem_rows(), L.owned_global_elem_rows()
+        xl = np.ascontiguousarray(x0g[loc])
+        xl[: own.start] = 0.123                       # stale ghost layers: setVars must refresh them from the owner
+        assert top.setVars(xl)
+        assert rel(top.getDensities()[own], ref["dens"][gown]) < 1e-14
+        np.testing.assert_allclose(top.getDensities(), ref["dens"][loc], rtol=0, atol=1e-14)   # ghost layers consistent too
+        assert abs(top.evaluateObjective() - ref["J"]) <= 1e-9 * abs(ref["J"])
+        assert rel(top.evaluateObjectiveGradient()[own], ref["grad"][gown]) < 1e-8
+        assert abs(top.evaluateConstraints()[0] - ref["c"]) < 1e-13
+        assert rel(top.evaluateConstraintsJacobian()[0][own], ref["jac"][gown]) < 1e-13
+        oc = V.OCOptimizer(top)
+        for k, (lam, xg, J) in enumerate(ref["steps"]):
+            oc.step()
+            assert abs(oc.lastLambda - lam) <= 1e-9 * lam, k
+            assert np.max(np.abs(top.getVars()[own] - xg[gown])) <= 1e-8, k
+            assert abs(top.evaluateObjective() - J) <= 1e-8 * J, k
+    run_ranks(world, body)
