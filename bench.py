@@ -229,9 +229,11 @@ def time_kapply(L, torch, dist, wl, W, K, seed, preheat_s=0.3):
 
     # untimed: every ring buffer touched, clocks ramped to their load state, then the W warm-up steps
     # (a fixed count derived from the GLOBAL size: the ranks must issue the same number of collective applies)
-    reps = max(1, min(500, int(preheat_s / (nsets * 3.0 * wl.nn_global / world / 60e9))))
+    reps = max(1, min(500 if world == 1 else 40, int(preheat_s / (nsets * 3.0 * wl.nn_global / world / 60e9))))
     for _ in range(reps):
         run(0, nsets)
+        if world > 1:
+            torch.cuda.synchronize()
     run(0, W)
     sync_all()
     launches0 = L.vfem_launch_count()
@@ -310,7 +312,15 @@ def our_arm(args):
     torch.cuda.set_device(local)
     _lib.check(_lib.lib().vfem_set_device(local))
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=180))
+        # a collective that never completes must not hold the box for the driver's whole limit
+        import signal
+        def _alarm(signum, frame):
+            sys.stderr.write("bench.py: rank %d made no progress for 900 s - aborting\n" % rank)
+            os._exit(3)
+        signal.signal(signal.SIGALRM, _alarm)
+        signal.alarm(900)
     W, K = args.warmup, args.steps
     hbm_peak, peak_src = measured_peaks()
     L = _lib.lib()

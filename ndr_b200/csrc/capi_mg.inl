@@ -39,7 +39,12 @@ int vfem_mg_apply_k_halo(vfem_mg_t h, double *u, double *out, int ms) {
     API_TRY WITH_MG(h, if (ms != VFEM_DEVICE) throw std::runtime_error("vfem_mg_apply_k_halo needs device arrays");
                     mg.template exchangeApplyFine<0>(u, nullptr, out);); API_CATCH }
 int vfem_mg_apply_k_halo_ring(vfem_mg_t h, double *const *us, double *const *outs, size_t nsets, size_t start, size_t count) {
-    API_TRY WITH_MG(h, for (size_t k = 0; k < count; ++k) mg.template exchangeApplyFine<0>(us[(start + k) % nsets], nullptr, outs[(start + k) % nsets]);); API_CATCH }
+    // at most 16 halo'd applies (each: an NCCL group + kernels on two streams) are kept in flight: two ranks that queue thousands of
+    // them without ever yielding were seen to stall each other (r02c); the wait costs ~1 % of a 16-apply burst
+    API_TRY WITH_MG(h, for (size_t k = 0; k < count; ++k) {
+                        mg.template exchangeApplyFine<0>(us[(start + k) % nsets], nullptr, outs[(start + k) % nsets]);
+                        if (mg.slab() && (k + 1) % 16 == 0 && k + 1 < count) VFEM_CUDA(cudaStreamSynchronize(mg.stream));
+                    }); API_CATCH }
 int vfem_mg_dot(vfem_mg_t h, const double *a, const double *b, int ms, double *result) {
     API_TRY WITH_MG(h, size_t n = mg.levelDofs(0); Staged st(mg.stream); const double *da = st.in(a, n, ms); const double *db = st.in(b, n, ms);
                     *result = mg.dot(da, db, n);); API_CATCH }

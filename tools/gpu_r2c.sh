@@ -1,16 +1,19 @@
 #!/bin/bash
-# round 2, multi-GPU call: N ranks (default 2): slab correctness vs 1 GPU, bench with / without graph replay, levels 3 / 4
+# multi-GPU call (N ranks, default 2); every command under a short timeout: a stalled collective must not hold the box
 N=${1:-2}
 O=gpurun_out/r2c_n$N
 mkdir -p $O
+export TORCH_NCCL_HEARTBEAT_TIMEOUT_SEC=120
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
-timeout 600 $TR --master-port 29511 tools/slab_check.py > $O/slab_check.log 2>&1; echo "rc=$?" >> $O/slab_check.log
-timeout 900 $TR --master-port 29512 bench.py --gpus $N --steps 20 --warmup 5 > $O/bench.json 2> $O/bench.err; echo "rc=$?" >> $O/bench.err
-VFEM_SLAB_NO_GRAPH=1 timeout 900 $TR --master-port 29513 bench.py --gpus $N --steps 20 --warmup 5 --no-extra > $O/bench_nograph.json 2>> $O/bench.err
-timeout 900 $TR --master-port 29514 bench.py --gpus $N --steps 20 --warmup 5 --no-extra --levels 4 > $O/bench_l4.json 2>> $O/bench.err
-timeout 900 $TR --master-port 29515 bench.py --gpus $N --steps 20 --warmup 5 --no-extra --levels 5 > $O/bench_l5.json 2>> $O/bench.err
-timeout 600 $TR --master-port 29516 bench.py --impl reference --gpus $N --steps 5 --warmup 3 > $O/bench_ref.json 2>> $O/bench.err
-tail -n 5 $O/slab_check.log $O/bench.err; for f in $O/bench*.json; do echo $f; python - "$f" <<'P'
+timeout 200 $TR --master-port 29511 tools/slab_check.py > $O/slab_check.log 2>&1; echo "rc=$?" >> $O/slab_check.log
+timeout 200 $TR --master-port 29512 bench.py --gpus $N --steps 20 --warmup 5 --no-extra --no-solve > $O/bench_apply.json 2> $O/bench_apply.err; echo "rc=$?" >> $O/bench_apply.err
+VFEM_NO_HALO_GRAPH=1 timeout 200 $TR --master-port 29517 bench.py --gpus $N --steps 20 --warmup 5 --no-extra --no-solve > $O/bench_apply_nohalograph.json 2>> $O/bench_apply.err; echo "rc=$?" >> $O/bench_apply.err
+timeout 300 $TR --master-port 29513 bench.py --gpus $N --steps 20 --warmup 5 --no-extra > $O/bench_solve.json 2> $O/bench_solve.err; echo "rc=$?" >> $O/bench_solve.err
+VFEM_SLAB_NO_GRAPH=1 timeout 300 $TR --master-port 29514 bench.py --gpus $N --steps 20 --warmup 5 --no-extra > $O/bench_solve_nograph.json 2>> $O/bench_solve.err; echo "rc=$?" >> $O/bench_solve.err
+timeout 300 $TR --master-port 29515 bench.py --gpus $N --steps 20 --warmup 5 --no-extra --levels 4 > $O/bench_l4.json 2>> $O/bench_solve.err; echo "rc=$?" >> $O/bench_solve.err
+timeout 500 $TR --master-port 29516 bench.py --gpus $N --steps 20 --warmup 5 > $O/bench_full.json 2> $O/bench_full.err; echo "rc=$?" >> $O/bench_full.err
+timeout 200 $TR --master-port 29518 bench.py --impl reference --gpus $N --steps 5 --warmup 3 > $O/bench_ref.json 2>> $O/bench_full.err
+grep "rc=" $O/*.err $O/slab_check.log; for f in $O/bench*.json; do echo $f; python - "$f" <<'P'
 import json,sys
 try:
     d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
