@@ -37,8 +37,7 @@ struct BlockTri {
             int dev = 0, sms = 148, per = 1;
             VFEM_CUDA(cudaGetDevice(&dev));
             VFEM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-            VFEM_CUDA(cudaFuncSetAttribute(blockTriFactorKernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFactorSmem)));
-            VFEM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, blockTriFactorKernel<N>, kFactorThreads, kFactorSmem));
+            VFEM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, blockTriFactorKernel<N>, kFactorThreads, 0));
             if (per < 1) throw std::runtime_error("blockTriFactorKernel does not fit on this device");
             factorBlocksMax = sms; // one CTA per SM: the kernel is bound by its grid barriers, not by occupancy
         }
@@ -50,7 +49,7 @@ struct BlockTri {
         for (int d = 1; d < N; ++d) fp.pn[d - 1] = g.n[d];
         Real *Dp = D.p, *trm = Trm.p, *tcm = Tcm.p; const Real *lo = Lo.p; int *inf = info.p;
         void *args[] = {&fp, &Dp, &lo, &trm, &tcm, &inf};
-        VFEM_CUDA(cudaLaunchCooperativeKernel((const void *)blockTriFactorKernel<N>, dim3(blocks), dim3(kFactorThreads), args, kFactorSmem, stream));
+        VFEM_CUDA(cudaLaunchCooperativeKernel((const void *)blockTriFactorKernel<N>, dim3(blocks), dim3(kFactorThreads), args, 0, stream));
         countLaunch();
     }
 

@@ -7,9 +7,9 @@
 // from BOTH ends of the plane sequence (ChainIdx, coarse_solve.cuh): the first half of the grid's CTAs eliminates the
 // planes 0..mid-1 downwards, the second half planes-1..mid+1 upwards, both meet at plane `mid`.
 //  * S_p^{-1} is formed IN PLACE by a blocked Gauss-Jordan inversion without pivoting (S_p is SPD; constrained dofs are
-//    identity rows).  Block size 64: every CTA inverts the 64x64 pivot block in shared memory itself (no broadcast
-//    step), then updates its share of the trailing 64x64 tiles  C_ij -= (F_i D^{-1}) R_j  (4x4 register tiles); a grid
-//    barrier; the pivot row / column panels; a grid barrier.  2 P^3 flops per plane, 2 ceil(P/64) grid barriers.
+//    identity rows).  Block size 32: every CTA inverts the 32x32 pivot block in shared memory itself (no broadcast
+//    step), then updates its share of the trailing 32x32 tiles  C_ij -= (F_i D^{-1}) R_j ; a grid barrier; the pivot
+//    row / column panels ; a grid barrier.  2 P^3 flops per plane, 2 ceil(P/32) grid barriers.
 //  * A_{p+1,p} couples a node only to the 3^(N-1) nodes around it in the neighbouring plane, so T = A S^{-1} and the
 //    Schur update T A^T are SPARSE-times-dense products (<= 3^(N-1) N terms per entry) instead of P^3 GEMMs.
 // Outputs are the arrays the chain-solve kernels (coarse_solve.cuh) read: S_p^{-1} (in D), T row- and column-major.
@@ -18,9 +18,8 @@
 
 namespace vfem {
 
-constexpr int kFB = 64, kFP = kFB + 1;  // Gauss-Jordan block size; shared-memory row pitch
-constexpr int kFactorThreads = 256;     // 16 x 16 threads, 4 x 4 entries of a 64 x 64 tile each
-constexpr size_t kFactorSmem = size_t(4) * kFB * kFP * sizeof(Real); // pivot (x2, ping-pong; the second doubles as F), G, R
+constexpr int kFB = 32;             // Gauss-Jordan block size
+constexpr int kFactorThreads = 256; // 32 rows x 8 column groups of 4
 
 template <int N>
 struct FactorParams {
@@ -58,95 +57,69 @@ __device__ __forceinline__ void planeNeighbours(const FactorParams<N> &fp, int i
 }
 
 // In-place inverse of the SPD matrix M (P x P, leading dimension P; nullptr = this team idles but keeps the barrier
-// count) by the team's CTAs [0, ncb); every CTA of the GRID calls this with the same P.  sm: kFactorSmem bytes.
-// 256 threads as 16 x 16, a thread owns the 4 x 4 entries (tx + 16 i, ty + 16 j) of a 64 x 64 tile: rows run along the
-// lanes (column-major M: coalesced; shared-memory rows at pitch 65: conflict-free), columns are warp-uniform broadcasts;
-// 0.5 shared-memory loads per FMA, so the tile products are bound by the FP64 pipe and not by LDS.
-__device__ __forceinline__ void gaussJordanInvert(Real *M, int P, int cb, int ncb, int *info, int plane, Real *sm) {
+// count) by the team's CTAs [0, ncb); every CTA of the GRID calls this with the same P.
+__device__ __forceinline__ void gaussJordanInvert(Real *M, int P, int cb, int ncb, int *info, int plane) {
     namespace cg = cooperative_groups;
     cg::grid_group grid = cg::this_grid();
-    typedef Real (*Tile)[kFP];
-    Tile sD = reinterpret_cast<Tile>(sm), sF = reinterpret_cast<Tile>(sm + kFB * kFP), sG = reinterpret_cast<Tile>(sm + 2 * kFB * kFP),
-         sR = reinterpret_cast<Tile>(sm + 3 * kFB * kFP);
-    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    __shared__ Real sD[kFB][kFB + 1], sG[kFB][kFB + 1], sF[kFB][kFB + 1], sR[kFB][kFB + 1];
+    const int tid = threadIdx.x, tr = tid & 31, tc = tid >> 5; // row, column group (columns 4 tc .. 4 tc + 3)
     const int nbk = (P + kFB - 1) / kFB;
-    auto loadTile = [&](Tile s, int r0, int c0, bool identityPad) {
-#pragma unroll 4
-        for (int q = 0; q < kFB * kFB / kFactorThreads; ++q) {
-            const int e = tid + q * kFactorThreads, r = e & (kFB - 1), c = e / kFB;
+    auto loadTile = [&](Real (&s)[kFB][kFB + 1], int r0, int c0, bool identityPad) {
+        for (int e = tid; e < kFB * kFB; e += kFactorThreads) {
+            const int r = e & 31, c = e >> 5;
             const bool in = r0 + r < P && c0 + c < P;
             s[r][c] = in ? __ldcg(M + size_t(r0 + r) + size_t(c0 + c) * P) : ((identityPad && r == c) ? 1.0 : 0.0);
-        }
-    };
-    // acc[i][j] (+)= sum_k A[tx + 16 i][k] * B[k][ty + 16 j]
-    auto tileProduct = [&](Tile A, Tile B, Real (&acc)[4][4]) {
-#pragma unroll 4
-        for (int k = 0; k < kFB; ++k) {
-            Real a[4], bq[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) { a[i] = A[tx + 16 * i][k]; bq[i] = B[k][ty + 16 * i]; }
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) acc[i][j] = fma(a[i], bq[j], acc[i][j]);
         }
     };
     for (int kb = 0; kb < nbk; ++kb) {
         const int k0 = kb * kFB;
         if (M) {
-            // ---- pivot block -> its inverse, in shared memory (unblocked Gauss-Jordan, every CTA for itself; the two pivot
-            // buffers ping-pong, so a step costs one barrier) ----
+            // ---- pivot block -> its inverse, in shared memory (unblocked Gauss-Jordan, every CTA for itself) ----
             __syncthreads();
             loadTile(sD, k0, k0, true);
             __syncthreads();
-            Tile cur = sD, nxt = sF;
             for (int k = 0; k < kFB; ++k) {
-                const Real d = cur[k][k];
+                const Real d = sD[k][k];
                 if (!(d > 0.0) && tid == 0 && cb == 0) atomicCAS(info, 0, plane + 1);
                 const Real piv = 1.0 / d;
-                Real fr[4], rc[4];
+                Real nv[4];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) { fr[i] = cur[tx + 16 * i][k]; rc[i] = cur[k][ty + 16 * i]; }
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const int r = tx + 16 * i, c = ty + 16 * j;
-                        Real v;
-                        if (r == k) v = (c == k) ? piv : rc[j] * piv;
-                        else v = (c == k) ? -fr[i] * piv : fma(-fr[i] * piv, rc[j], cur[r][c]);
-                        nxt[r][c] = v;
-                    }
+                for (int q = 0; q < 4; ++q) {
+                    const int c = 4 * tc + q;
+                    const Real f = sD[tr][k], rk = sD[k][c];
+                    if (tr == k) nv[q] = (c == k) ? piv : rk * piv;
+                    else nv[q] = (c == k) ? -f * piv : fma(-f * piv, rk, sD[tr][c]);
+                }
                 __syncthreads();
-                Tile t2 = cur; cur = nxt; nxt = t2;
-            } // kFB is even: the inverse ends in sD, sF is free again
-            // ---- trailing tiles (i, j), i != kb, j != kb:  C -= (F_i D^-1) R_j ; the R tile and the C entries of the NEXT
-            // tile are fetched into registers before the arithmetic of the current one ----
+#pragma unroll
+                for (int q = 0; q < 4; ++q) sD[tr][4 * tc + q] = nv[q];
+                __syncthreads();
+            }
+            // ---- trailing tiles (i, j), i != kb, j != kb:  C -= (F_i D^-1) R_j ----
             const int nt = (nbk - 1) * (nbk - 1);
             const int t0 = int((long long)cb * nt / ncb), t1 = int((long long)(cb + 1) * nt / ncb);
+            // the R tile and the C entries of the NEXT tile are fetched into registers before the arithmetic of the current
+            // one (a tile is 3 dependent L2 round trips otherwise: the loop is latency-, not FP64-bound)
             auto tileOf = [&](int t, int &i, int &j) {
                 const int ii = t / (nbk - 1), jj = t - ii * (nbk - 1);
                 i = ii + (ii >= kb); j = jj + (jj >= kb);
             };
-            constexpr int LQ = kFB * kFB / kFactorThreads; // 16 entries per thread
-            auto fetchR = [&](int j, Real (&rr)[LQ]) {
+            auto fetchR = [&](int j, Real (&rr)[4]) {
 #pragma unroll
-                for (int q = 0; q < LQ; ++q) {
-                    const int e = tid + q * kFactorThreads, r = k0 + (e & (kFB - 1)), c = j * kFB + e / kFB;
+                for (int q = 0; q < 4; ++q) {
+                    const int e = tid + q * kFactorThreads, r = k0 + (e & 31), c = j * kFB + (e >> 5);
                     rr[q] = (r < P && c < P) ? __ldcg(M + size_t(r) + size_t(c) * P) : 0.0;
                 }
             };
-            auto fetchC = [&](int i, int j, Real (&cv)[4][4]) {
+            auto fetchC = [&](int i, int j, Real (&cv)[4]) {
 #pragma unroll
-                for (int a = 0; a < 4; ++a)
-#pragma unroll
-                    for (int bq = 0; bq < 4; ++bq) {
-                        const int r = i * kFB + tx + 16 * a, c = j * kFB + ty + 16 * bq;
-                        cv[a][bq] = (r < P && c < P) ? __ldcg(M + size_t(r) + size_t(c) * P) : 0.0;
-                    }
+                for (int q = 0; q < 4; ++q) {
+                    const int r = i * kFB + tr, c = j * kFB + 4 * tc + q;
+                    cv[q] = (r < P && c < P) ? __ldcg(M + size_t(r) + size_t(c) * P) : 0.0;
+                }
             };
             int curI = -1, i = 0, j = 0;
-            Real rr[LQ], cn[4][4];
+            Real rr[4], cn[4];
             if (t0 < t1) { tileOf(t0, i, j); fetchR(j, rr); fetchC(i, j, cn); }
             for (int t = t0; t < t1; ++t) {
                 tileOf(t, i, j);
@@ -154,32 +127,35 @@ __device__ __forceinline__ void gaussJordanInvert(Real *M, int P, int cb, int nc
                 if (i != curI) {
                     loadTile(sF, i * kFB, k0, false);
                     __syncthreads();
-                    Real g[4][4] = {};
-                    tileProduct(sF, sD, g);
+                    Real g[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll 8
+                    for (int k = 0; k < kFB; ++k) {
+                        const Real f = sF[tr][k];
 #pragma unroll
-                    for (int a = 0; a < 4; ++a)
+                        for (int q = 0; q < 4; ++q) g[q] = fma(f, sD[k][4 * tc + q], g[q]);
+                    }
 #pragma unroll
-                        for (int bq = 0; bq < 4; ++bq) sG[tx + 16 * a][ty + 16 * bq] = g[a][bq];
+                    for (int q = 0; q < 4; ++q) sG[tr][4 * tc + q] = g[q];
                     curI = i;
                 }
-                Real cv[4][4];
+                Real cv[4];
 #pragma unroll
-                for (int q = 0; q < LQ; ++q) { const int e = tid + q * kFactorThreads; sR[e & (kFB - 1)][e / kFB] = rr[q]; }
-#pragma unroll
-                for (int a = 0; a < 4; ++a)
-#pragma unroll
-                    for (int bq = 0; bq < 4; ++bq) cv[a][bq] = cn[a][bq];
+                for (int q = 0; q < 4; ++q) { const int e = tid + q * kFactorThreads; sR[e & 31][e >> 5] = rr[q]; cv[q] = cn[q]; }
                 if (t + 1 < t1) { int i2, j2; tileOf(t + 1, i2, j2); fetchR(j2, rr); fetchC(i2, j2, cn); }
                 __syncthreads();
-                Real acc[4][4] = {};
-                tileProduct(sG, sR, acc);
+                const int r = i * kFB + tr;
+                Real acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll 8
+                for (int k = 0; k < kFB; ++k) {
+                    const Real gk = sG[tr][k];
 #pragma unroll
-                for (int a = 0; a < 4; ++a)
+                    for (int q = 0; q < 4; ++q) acc[q] = fma(gk, sR[k][4 * tc + q], acc[q]);
+                }
 #pragma unroll
-                    for (int bq = 0; bq < 4; ++bq) {
-                        const int r = i * kFB + tx + 16 * a, c = j * kFB + ty + 16 * bq;
-                        if (r < P && c < P) M[size_t(r) + size_t(c) * P] = cv[a][bq] - acc[a][bq];
-                    }
+                for (int q = 0; q < 4; ++q) {
+                    const int c = j * kFB + 4 * tc + q;
+                    if (r < P && c < P) M[size_t(r) + size_t(c) * P] = cv[q] - acc[q];
+                }
             }
         }
         grid.sync();
@@ -190,27 +166,28 @@ __device__ __forceinline__ void gaussJordanInvert(Real *M, int P, int cb, int nc
                 __syncthreads();
                 if (t == nt - 1) {
 #pragma unroll
-                    for (int a = 0; a < 4; ++a)
-#pragma unroll
-                        for (int bq = 0; bq < 4; ++bq) {
-                            const int r = k0 + tx + 16 * a, c = k0 + ty + 16 * bq;
-                            if (r < P && c < P) M[size_t(r) + size_t(c) * P] = sD[tx + 16 * a][ty + 16 * bq];
-                        }
+                    for (int q = 0; q < 4; ++q) {
+                        const int r = k0 + tr, c = k0 + 4 * tc + q;
+                        if (r < P && c < P) M[size_t(r) + size_t(c) * P] = sD[tr][4 * tc + q];
+                    }
                     continue;
                 }
                 const bool rowPanel = t < nbk - 1;
                 const int o = rowPanel ? t : t - (nbk - 1), blk = o + (o >= kb);
                 loadTile(sR, rowPanel ? k0 : blk * kFB, rowPanel ? blk * kFB : k0, false);
                 __syncthreads();
-                Real acc[4][4] = {};
-                if (rowPanel) tileProduct(sD, sR, acc); else tileProduct(sR, sD, acc);
+                Real acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll 8
+                for (int k = 0; k < kFB; ++k) {
 #pragma unroll
-                for (int a = 0; a < 4; ++a)
+                    for (int q = 0; q < 4; ++q)
+                        acc[q] = rowPanel ? fma(sD[tr][k], sR[k][4 * tc + q], acc[q]) : fma(sR[tr][k], sD[k][4 * tc + q], acc[q]);
+                }
 #pragma unroll
-                    for (int bq = 0; bq < 4; ++bq) {
-                        const int r = (rowPanel ? k0 : blk * kFB) + tx + 16 * a, c = (rowPanel ? blk * kFB : k0) + ty + 16 * bq;
-                        if (r < P && c < P) M[size_t(r) + size_t(c) * P] = rowPanel ? acc[a][bq] : -acc[a][bq];
-                    }
+                for (int q = 0; q < 4; ++q) {
+                    const int r = (rowPanel ? k0 : blk * kFB) + tr, c = (rowPanel ? blk * kFB : k0) + 4 * tc + q;
+                    if (r < P && c < P) M[size_t(r) + size_t(c) * P] = rowPanel ? acc[q] : -acc[q];
+                }
             }
         }
         grid.sync();
@@ -224,8 +201,6 @@ static __global__ void __launch_bounds__(kFactorThreads) blockTriFactorKernel(Fa
                                                                               Real *Trm, Real *Tcm, int *info) {
     namespace cg = cooperative_groups;
     cg::grid_group grid = cg::this_grid();
-    extern __shared__ __align__(16) unsigned char factorRaw[];
-    Real *fsm = reinterpret_cast<Real *>(factorRaw);
     const int P = fp.P, planes = fp.planes, mid = fp.mid;
     const size_t PP = size_t(P) * P;
     const ChainIdx ci{planes, mid};
@@ -243,7 +218,7 @@ static __global__ void __launch_bounds__(kFactorThreads) blockTriFactorKernel(Fa
         for (int s = 0; s < (serial ? ci.len(cc) : S); ++s) {
             const bool active = !spare && s < ci.len(cc);
             const int p = ci.plane(cc, s);
-            gaussJordanInvert(active ? D + PP * p : nullptr, P, cb, ncb, info, p, fsm);
+            gaussJordanInvert(active ? D + PP * p : nullptr, P, cb, ncb, info, p);
             // ---- T = A S^-1 (chain 0: T_{p+1} = A_{p+1,p} S_p^-1, block p; chain 1: U_{p-1} = A_{p,p-1}^T S_p^-1, block p-1) ----
             const int q = cc == 0 ? p : p - 1;
             if (active) { // one warp per row i of T: its <= 3^(N-1) N coefficients of A first, then lanes over the columns
@@ -296,7 +271,7 @@ static __global__ void __launch_bounds__(kFactorThreads) blockTriFactorKernel(Fa
             }
         }
     }
-    gaussJordanInvert(spare ? nullptr : (c == 0 ? D + PP * mid : nullptr), P, cb, ncb, info, mid, fsm);
+    gaussJordanInvert(spare ? nullptr : (c == 0 ? D + PP * mid : nullptr), P, cb, ncb, info, mid);
 }
 
 } // namespace vfem

@@ -229,7 +229,7 @@ int vfem_top_set_vars(vfem_top_t h, const double *x, int ms, int force, int *cha
     API_TRY WITH_TOP(h, bool ch = tp.setVars(x, MemSpace(ms), force != 0); if (changed) *changed = ch ? 1 : 0;); API_CATCH }
 int vfem_top_get_vars(vfem_top_t h, int which, double *out, int ms) {
     int rc = 0; WITH_TOP(h, if (which >= int(tp.cached.size())) { g_err = "filter stage out of range"; return 1; }
-                         auto &c = which < 0 ? tp.cached.back() : tp.cached[which]; rc = copyOut(c.p, out, c.n, ms);); return rc; }
+                         auto &c = which < 0 ? tp.cached.back() : tp.cached[which]; rc = copyOut(c.p, out, tp.numVars(), ms);); return rc; }
 int vfem_top_objective(vfem_top_t h, double *J) { API_TRY WITH_TOP(h, *J = tp.evaluateObjective();); API_CATCH }
 int vfem_top_objective_gradient(vfem_top_t h, double *g, int ms) {
     API_TRY WITH_TOP(h, Staged st(tp.sim->stream); double *dg = st.out(g, tp.numVars(), ms); tp.evaluateObjectiveGradient(dg); st.finish();); API_CATCH }
