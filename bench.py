@@ -227,6 +227,10 @@ def time_kapply(L, torch, dist, wl, W, K, seed, preheat_s=0.3):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def trace(msg):
+        if os.environ.get("VFEM_BENCH_TRACE"):
+            print("[rank %s %.2f] time_kapply %s" % (os.environ.get("RANK", "0"), time.time() % 1000, msg), file=sys.stderr, flush=True)
+
     # untimed: every ring buffer touched, clocks ramped to their load state, then the W warm-up steps
     # (a fixed count derived from the GLOBAL size: the ranks must issue the same number of collective applies)
     reps = max(1, min(500 if world == 1 else 40, int(preheat_s / (nsets * 3.0 * wl.nn_global / world / 60e9))))
@@ -234,14 +238,17 @@ def time_kapply(L, torch, dist, wl, W, K, seed, preheat_s=0.3):
         run(0, nsets)
         if world > 1:
             torch.cuda.synchronize()
+    trace("preheat done (%d x %d applies)" % (reps, nsets))
     run(0, W)
     sync_all()
+    trace("warm-up done")
     launches0 = L.vfem_launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     run(W, K)
     ev1.record()
     sync_all()
+    trace("timed region done")
     ms = ev0.elapsed_time(ev1)
     launches = L.vfem_launch_count() - launches0
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")

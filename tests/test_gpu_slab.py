@@ -192,7 +192,7 @@ def test_slab_topology_optimization_iteration(oracle_mod, grid, levels, world):
         top = V.TopologyOptimizationProblem(s.tps, obj, [V.TotalVolumeConstraint(vol)], [V.SmoothingFilter(), V.ProjectionFilter()])
         obj.tol = 1e-11
         loc, own, gown = L.elem_slice(), L.owned_elem_rows(), L.owned_global_elem_rows()
-        xl = np.ascontiguousarray(x0g[loc])
+        xl = x0g[loc].copy()                          # a private copy: the ranks are threads sharing x0g
         xl[: own.start] = 0.123                       # stale ghost layers: setVars must refresh them from the owner
         assert top.setVars(xl)
         assert rel(top.getDensities()[own], ref["dens"][gown]) < 1e-14

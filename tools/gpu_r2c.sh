@@ -1,19 +1,35 @@
 #!/bin/bash
-# multi-GPU call (N ranks, default 2); every command under a short timeout: a stalled collective must not hold the box
+# multi-GPU call (N ranks, default 2).  Every command runs under a short timeout and the script stops at the first one that
+# times out: a stalled collective must not hold the box.
 N=${1:-2}
 O=gpurun_out/r2c_n$N
 mkdir -p $O
-export TORCH_NCCL_HEARTBEAT_TIMEOUT_SEC=120
+export TORCH_NCCL_HEARTBEAT_TIMEOUT_SEC=120 VFEM_BENCH_TRACE=1
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
-timeout 200 $TR --master-port 29511 tools/slab_check.py > $O/slab_check.log 2>&1; echo "rc=$?" >> $O/slab_check.log
-timeout 200 $TR --master-port 29512 bench.py --gpus $N --steps 20 --warmup 5 --no-extra --no-solve > $O/bench_apply.json 2> $O/bench_apply.err; echo "rc=$?" >> $O/bench_apply.err
-VFEM_NO_HALO_GRAPH=1 timeout 200 $TR --master-port 29517 bench.py --gpus $N --steps 20 --warmup 5 --no-extra --no-solve > $O/bench_apply_nohalograph.json 2>> $O/bench_apply.err; echo "rc=$?" >> $O/bench_apply.err
-timeout 300 $TR --master-port 29513 bench.py --gpus $N --steps 20 --warmup 5 --no-extra > $O/bench_solve.json 2> $O/bench_solve.err; echo "rc=$?" >> $O/bench_solve.err
-VFEM_SLAB_NO_GRAPH=1 timeout 300 $TR --master-port 29514 bench.py --gpus $N --steps 20 --warmup 5 --no-extra > $O/bench_solve_nograph.json 2>> $O/bench_solve.err; echo "rc=$?" >> $O/bench_solve.err
-timeout 300 $TR --master-port 29515 bench.py --gpus $N --steps 20 --warmup 5 --no-extra --levels 4 > $O/bench_l4.json 2>> $O/bench_solve.err; echo "rc=$?" >> $O/bench_solve.err
-timeout 500 $TR --master-port 29516 bench.py --gpus $N --steps 20 --warmup 5 > $O/bench_full.json 2> $O/bench_full.err; echo "rc=$?" >> $O/bench_full.err
-timeout 200 $TR --master-port 29518 bench.py --impl reference --gpus $N --steps 5 --warmup 3 > $O/bench_ref.json 2>> $O/bench_full.err
-grep "rc=" $O/*.err $O/slab_check.log; for f in $O/bench*.json; do echo $f; python - "$f" <<'P'
+PORT=29510
+step() { # name, time limit, command...
+  local name=$1 lim=$2; shift 2
+  [ -e $O/STOP ] && return
+  PORT=$((PORT + 1))
+  ( time timeout $lim "$@" ) > $O/$name.out 2> $O/$name.err
+  local rc=$?
+  echo "rc=$rc" >> $O/$name.err
+  if [ $rc -eq 124 ] || [ $rc -eq 137 ]; then echo "$name timed out" > $O/STOP; fi
+}
+step slab_check 200 $TR --master-port $PORT tools/slab_check.py
+step bench_apply 200 $TR --master-port $((PORT + 1)) bench.py --gpus $N --steps 20 --warmup 5 --no-extra --no-solve
+if [ -e $O/STOP ]; then   # diagnose: the same without the captured halo-shift + apply graph
+  rm -f $O/STOP
+  VFEM_NO_HALO_GRAPH=1 step bench_apply_nohalograph 200 $TR --master-port $((PORT + 1)) bench.py --gpus $N --steps 20 --warmup 5 --no-extra --no-solve
+  echo "halo graph hang" >> $O/STOP
+fi
+step bench_solve 300 $TR --master-port $((PORT + 1)) bench.py --gpus $N --steps 20 --warmup 5 --no-extra
+VFEM_SLAB_NO_GRAPH=1 step bench_solve_nograph 300 $TR --master-port $((PORT + 1)) bench.py --gpus $N --steps 20 --warmup 5 --no-extra
+step bench_l4 300 $TR --master-port $((PORT + 1)) bench.py --gpus $N --steps 20 --warmup 5 --no-extra --levels 4
+step bench_full 500 $TR --master-port $((PORT + 1)) bench.py --gpus $N --steps 20 --warmup 5
+step bench_ref 200 $TR --master-port $((PORT + 1)) bench.py --impl reference --gpus $N --steps 5 --warmup 3
+cat $O/STOP 2>/dev/null; grep "rc=\|^real" $O/*.err | tr '\n' ' '; echo
+for f in $O/bench*.out; do echo $f; python - "$f" <<'P'
 import json,sys
 try:
     d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
@@ -21,3 +37,4 @@ try:
 except Exception as e: print('ERR',e)
 P
 done
+tail -n 5 $O/slab_check.out
