@@ -272,7 +272,8 @@ def kernel_label(tps):
     if not info["march"]:
         return "applyFineKernel<3,0> (per-node gather)"
     ry, zt = MARCH_SHAPES[info["tile_shape"]] if info["tile_shape"] < len(MARCH_SHAPES) else (0, 0)
-    return "applyMarchKernel<MODE=0, SPARSE=%s, RY=%d, ZT=%d> grid (%d,%d,%d), %d layers per chunk" % (
+    name = "applyMarchKernel" if os.environ.get("VFEM_APPLY_VARIANT") == "4" else "applyMarchTmaKernel"   # sim.cu: variant 4 = first generation
+    return name + "<MODE=0, SPARSE=%s, RY=%d, ZT=%d> grid (%d,%d,%d), %d layers per chunk" % (
         "true" if info["k0_structure"] == 2 else "false", ry, zt, info["grid_x"], info["grid_y"], info["grid_z"], info["layers_per_chunk"])
 
 

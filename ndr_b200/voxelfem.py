@@ -12,6 +12,7 @@ import json
 import numpy as np
 
 from ._lib import FILTER_CB, PCG_CB, RESIDUAL_CB, SOLVE_CB, check, lib
+from .benchmark import timed as _timed
 
 HOST, DEVICE = 0, 1
 
@@ -247,6 +248,7 @@ class TensorProductSimulator:
         return v.value
 
     # --- operators ---
+    @_timed(lambda self: "applyK " + "x".join(str(int(e)) for e in self._elems))
     def applyK(self, u, out=None):
         a = _Arg(u, self.numDoFs())
         if a.ms == DEVICE:

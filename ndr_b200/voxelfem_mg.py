@@ -7,6 +7,7 @@ import numpy as np
 from . import voxelfem as _v
 from ._lib import FILTER_CB, PCG_CB, RESIDUAL_CB, SOLVE_CB, check, lib
 from .voxelfem import DEVICE, HOST, _Arg, _dev_ptr, _is_device, _np, _ptr
+from .benchmark import timed as _timed
 
 
 class _LevelView:
@@ -127,6 +128,7 @@ class MultigridSolver:
         check(lib().vfem_mg_debug_get(self._h, l, None, _ptr(b)))
         return b
 
+    @_timed("MG Solver")
     def solve(self, u, f, numSteps, numSmoothingSteps, stiffnessUpdated=False, zeroDirichlet=False, it_callback=None,
               fullMultigrid=False):
         n, shape = self._n(0), self._shape(0)
@@ -138,6 +140,7 @@ class MultigridSolver:
                                   cb, None, int(fullMultigrid), _ptr(out), HOST))
         return out
 
+    @_timed("CG Iterations")
     def preconditionedConjugateGradient(self, u, b, maxIter, tol, it_callback=None, mgIterations=1, mgSmoothingIterations=1,
                                         fullMultigrid=False, out=None, return_info=False):
         n, shape = self._n(0), self._shape(0)

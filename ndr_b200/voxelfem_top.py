@@ -6,6 +6,7 @@ import numpy as np
 
 from ._lib import FILTER_CB, check, lib
 from .voxelfem import DEVICE, HOST, _Arg, _dev_ptr, _is_device, _np, _ptr
+from .benchmark import timed as _timed
 
 _SMOOTHING, _PROJECTION, _CALLBACK = 0, 1, 2
 
@@ -214,6 +215,7 @@ class TopologyOptimizationProblem:
                 f._error = None
                 raise e
 
+    @_timed("setVars")
     def setVars(self, x, forceUpdate=False):
         a = _Arg(x, self.numVars())
         ch = C.c_int(0)
@@ -236,11 +238,13 @@ class TopologyOptimizationProblem:
     def getDensities(self, out=None):
         return self._get(-1, out)
 
+    @_timed("evaluateObjective")
     def evaluateObjective(self):
         J = C.c_double()
         check(lib().vfem_top_objective(self._h, C.byref(J)))
         return J.value
 
+    @_timed("evaluateObjectiveGradient")
     def evaluateObjectiveGradient(self, out=None):
         """numpy array by default; pass a float64 CUDA array as `out` to receive the gradient with no copy."""
         if out is not None and _is_device(out):
@@ -252,11 +256,13 @@ class TopologyOptimizationProblem:
         self._reraise(); check(rc)
         return g
 
+    @_timed("evaluateConstraints")
     def evaluateConstraints(self):
         c = np.empty(len(self._constraints))
         check(lib().vfem_top_constraints(self._h, _ptr(c)))
         return c
 
+    @_timed("evaluateConstraintsJacobian")
     def evaluateConstraintsJacobian(self):
         j = np.empty((len(self._constraints), self.numVars()))
         rc = lib().vfem_top_constraints_jacobian(self._h, _ptr(j), HOST)
@@ -272,6 +278,7 @@ class OCOptimizer:
         check(lib().vfem_oc_reset(problem._h))
         self.lastLambda, self.lastEvaluations = 0.0, 0
 
+    @_timed("OC step")
     def step(self, m=0.2, ctol=1e-6):
         lam, nev = C.c_double(), C.c_int()
         rc = lib().vfem_oc_step(self._p._h, float(m), float(ctol), C.byref(lam), C.byref(nev))

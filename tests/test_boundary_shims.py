@@ -165,3 +165,25 @@ def test_reference_helper_modules_import_against_the_shims(shim_path):
     with pytest.raises(RuntimeError, match="no CUDA device|CUDA"):
         if pyVoxelFEM.TensorProductSimulator([1, 1], [[0, 0], [1, 1]], [4, 4]):
             raise RuntimeError("CUDA device present")  # on a GPU box the constructor succeeds: still fine
+
+
+@pytest.mark.gpu
+def test_benchmark_sections_carry_the_reference_names(capsys):
+    """after benchmark_reset() the bound calls record the reference's own section names (TPS.hh:907, MG.hh:693, Problem.hh:43-132,
+    OptimalityCriterion.hh:42); before it nothing is recorded (no device synchronisation in an unprofiled run)"""
+    import numpy as np
+    import ndr_b200.pyVoxelFEM as V
+    from ndr_b200 import benchmark as B
+    B._enabled = False; B._sections.clear()
+    tps = V.TensorProductSimulator([1, 1, 1], [np.zeros(3), np.array([2.0, 1.0, 1.0])], [16, 8, 8])
+    u = np.random.default_rng(0).standard_normal((tps.numNodes(), 3))
+    tps.applyK(u)
+    assert B.to_dict() == {}
+    V.benchmark_reset()
+    tps.applyK(u)
+    tps.applyK(u)
+    d = B.to_dict()
+    assert d["applyK 16x8x8"]["calls"] == 2 and d["applyK 16x8x8"]["time"] > 0
+    V.benchmark_report()
+    assert "applyK 16x8x8" in capsys.readouterr().out
+    B._enabled = False; B._sections.clear()
