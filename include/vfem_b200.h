@@ -166,6 +166,15 @@ int vfem_oc_step(vfem_top_t h, double m, double ctol, double *lambda, int *num_e
 /* pyVoxelFEM.applyFilter(filter, x) (VoxelFEM.cc:275-281); x has prod(dims) entries, host memory */
 int vfem_apply_filter(int filter_type, double param, int ndim, const size_t *dims, const double *x, double *out);
 
+/* ---- allocation-free entry point ---------------------------------------------------------------------------------- */
+/* NO counterpart in the reference: added for callers that must not trigger
+   cudaMalloc (CUDA-graph capture, serving loops).  result_device[0] = a . b for two device arrays of n doubles, on the
+   legacy default stream, asynchronously; the reduction scratch is a static __device__ array of 64.25 KB per GPU
+   (ndr_b200/csrc/no_alloc.cu), so the call allocates nothing and n is limited to vfem_dot_no_alloc_max_n() = 33 554 432
+   entries (larger n: error).  All calls share that array: calls that overlap on the GPU race. */
+int vfem_dot_no_alloc(const double *a_device, const double *b_device, size_t n, double *result_device);
+size_t vfem_dot_no_alloc_max_n(void);
+
 #ifdef __cplusplus
 }
 #endif

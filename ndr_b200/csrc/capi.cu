@@ -64,6 +64,10 @@ struct Staged {
 #define WITH_OBJ(h, BODY) do { ObjH *hh_ = (ObjH *)(h); if (hh_->dim == 2) { constexpr int N = 2; auto &ob = *hh_->o2; (void)N; BODY } else { constexpr int N = 3; auto &ob = *hh_->o3; (void)N; BODY } } while (0)
 #define WITH_TOP(h, BODY) do { TopH *hh_ = (TopH *)(h); if (hh_->dim == 2) { constexpr int N = 2; auto &tp = *hh_->p2; (void)N; BODY } else { constexpr int N = 3; auto &tp = *hh_->p3; (void)N; BODY } } while (0)
 
+namespace vfem {
+void setLastError(const std::string &msg) { g_err = msg; } // for entry points defined in other files (no_alloc.cu)
+}
+
 extern "C" {
 
 const char *vfem_last_error(void) { return g_err.c_str(); }
