@@ -211,6 +211,10 @@ def time_kapply(L, torch, dist, wl, W, K, seed, preheat_s=0.3):
     stream, which is also torch's current stream here); max over ranks.  Returns (ms total over K steps, ms per kernel alone, launches)."""
     world = wl.world
     nsets = max(2, int(np.ceil(2.5 * L2_BYTES / (16 * 3 * wl.nn_l))))  # ring of u/Ku pairs larger than L2
+    if world > 1:   # the slabs differ in size (ghost layers): every rank must issue the SAME number of collective applies
+        t = torch.tensor([nsets], dtype=torch.int64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        nsets = int(t.item())
     gen = torch.Generator(device="cuda"); gen.manual_seed(seed)
     us = [torch.randn(wl.nn_l, 3, dtype=torch.float64, device="cuda", generator=gen) for _ in range(nsets)]
     outs = [torch.zeros(wl.nn_l, 3, dtype=torch.float64, device="cuda") for _ in range(nsets)]
@@ -226,6 +230,10 @@ def time_kapply(L, torch, dist, wl, W, K, seed, preheat_s=0.3):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    if os.environ.get("VFEM_BENCH_TRACE"):
+        import faulthandler
+        faulthandler.dump_traceback_later(45, exit=False)   # where is a rank that never leaves the preheat?
 
     def trace(msg):
         if os.environ.get("VFEM_BENCH_TRACE"):

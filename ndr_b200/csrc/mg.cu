@@ -265,7 +265,7 @@ void MG<N>::exchangeApplyFine(Real *u, const Real *b, Real *out) {
     syncMasks();
     // The overlapped form is 1 NCCL group + 3 kernel launches + 4 event operations on two streams: launch-bound next to a
     // 20 us kernel.  Its SECOND call with the same arrays captures it into a CUDA graph (fork / join included), later calls replay it.
-    if (useGraphs && comm->graphSafe() && comm->sideStreamSafe() && !getenv("VFEM_NO_HALO_GRAPH")) {
+    if (useGraphs && comm->graphSafe() && comm->sideStreamSafe() && !getenv("VFEM_NO_HALO_GRAPH") && !getenv("VFEM_TRACE_HALO")) {
         HaloGraphKey key{u, b, out, MODE, sim->k0Version, sim->applyVariant};
         auto it = haloGraphs.find(key);
         if (it == haloGraphs.end()) {
@@ -315,12 +315,25 @@ void MG<N>::exchangeApplyFineBody(Real *u, const Real *b, Real *out) {
         VFEM_CUDA(cudaStreamWaitEvent(hs, haloFork, 0));
     }
     const size_t pd = size_t(g.ninc[0]) * N;
+    // VFEM_TRACE_HALO=1 (diagnosis of a stalled exchange): synchronise after every part and say which one was reached
+    static const bool traceHalo = getenv("VFEM_TRACE_HALO") != nullptr;
+    static unsigned long long traceCall = 0;
+    auto mark = [&](const char *what, cudaStream_t s) {
+        if (!traceHalo) return;
+        fprintf(stderr, "[halo rank %d call %llu] %s issued\n", comm->rank, traceCall, what); fflush(stderr);
+        VFEM_CUDA(cudaStreamSynchronize(s));
+        fprintf(stderr, "[halo rank %d call %llu] %s done\n", comm->rank, traceCall, what); fflush(stderr);
+    };
+    if (traceHalo) ++traceCall;
     comm->shift(u + size_t(o1) * pd, below ? u + size_t(o0 - 1) * pd : u, u + size_t(o0) * pd, above ? u + size_t(o1 + 1) * pd : u, pd, true, true, hs);
+    mark("shift", hs);
     const uint8_t *mask = maskOf(*this, 0);
     sim->template applyFineRange<MODE>(u, b, mask, out, below ? o0 : 0, above ? o1 : E0, stream, (below ? 1 : 0) | (above ? 2 : 0));
+    mark("interior apply", stream);
     // the thin boundary views follow the shift on ITS stream: they share the SMs with the tail of the interior launch
     if (below) sim->template applyFineRange<MODE>(u, b, mask, out, o0 - 1, o0 + 1, hs, 3);
     if (above) sim->template applyFineRange<MODE>(u, b, mask, out, o1 - 1, o1 + 1, hs, 3);
+    mark("boundary views", hs);
     if (hs != stream) {
         VFEM_CUDA(cudaEventRecord(haloJoin, hs));
         VFEM_CUDA(cudaStreamWaitEvent(stream, haloJoin, 0));

@@ -4,7 +4,7 @@
 N=${1:-2}
 O=gpurun_out/r2c_n$N
 mkdir -p $O
-export TORCH_NCCL_HEARTBEAT_TIMEOUT_SEC=120 VFEM_BENCH_TRACE=1
+export TORCH_NCCL_HEARTBEAT_TIMEOUT_SEC=120
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 PORT=29510
 step() { # name, time limit, command...
@@ -16,7 +16,7 @@ step() { # name, time limit, command...
   echo "rc=$rc" >> $O/$name.err
   if [ $rc -eq 124 ] || [ $rc -eq 137 ]; then echo "$name timed out" > $O/STOP; fi
 }
-step slab_check 200 $TR --master-port $PORT tools/slab_check.py
+[ -z "$SKIP_SLAB_CHECK" ] && step slab_check 200 $TR --master-port $PORT tools/slab_check.py
 step bench_apply 200 $TR --master-port $((PORT + 1)) bench.py --gpus $N --steps 20 --warmup 5 --no-extra --no-solve
 if [ -e $O/STOP ]; then   # diagnose: the same without the captured halo-shift + apply graph
   rm -f $O/STOP
