@@ -264,8 +264,10 @@ void MG<N>::exchangeApplyFine(Real *u, const Real *b, Real *out) {
     sim->moduli(); // a stale E(rho) is refreshed on the solver stream BEFORE the fork
     syncMasks();
     // The overlapped form is 1 NCCL group + 3 kernel launches + 4 event operations on two streams: launch-bound next to a
-    // 20 us kernel.  Its SECOND call with the same arrays captures it into a CUDA graph (fork / join included), later calls replay it.
-    if (useGraphs && comm->graphSafe() && comm->sideStreamSafe() && !getenv("VFEM_NO_HALO_GRAPH") && !getenv("VFEM_TRACE_HALO")) {
+    // 20 us kernel.  With VFEM_HALO_GRAPH=1 its SECOND call with the same arrays captures it into a CUDA graph (fork / join
+    // included) and later calls replay it.  Measured on 2 x B200 (gpurun r2c): the replay is SLOWER than the plain launches
+    // (37.8 us against 28.1 us per halo'd apply of 128x64x64 layers per rank), so it is opt-in.
+    if (useGraphs && comm->graphSafe() && comm->sideStreamSafe() && getenv("VFEM_HALO_GRAPH") && !getenv("VFEM_TRACE_HALO")) {
         HaloGraphKey key{u, b, out, MODE, sim->k0Version, sim->applyVariant};
         auto it = haloGraphs.find(key);
         if (it == haloGraphs.end()) {
