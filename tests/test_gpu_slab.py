@@ -208,3 +208,42 @@ def test_slab_topology_optimization_iteration(oracle_mod, grid, levels, world):
             assert np.max(np.abs(top.getVars()[own] - xg[gown])) <= 1e-8, k
             assert abs(top.evaluateObjective() - J) <= 1e-8 * J, k
     run_ranks(world, body)
+
+
+@pytest.mark.parametrize("grid,levels,world", [([64, 32, 16], 2, 2), ([64, 32, 16], 3, 4), ([64, 32, 16], 3, 8)])
+def test_slab_mg_pcg_bridge(oracle_mod, grid, levels, world):
+    """BASELINE config 3's boundary conditions on slabs (bridge.bc: a clamped face on rank 0, an x-roller face on the LAST
+    rank, a force region that spans every rank): same iteration count as the oracle's undecomposed solve at the production
+    tolerance, converged solution equal"""
+    from ndr_b200.slab import SlabSolver, ThreadHostSum, make_thread_comms
+    dom, bc = [4.0, 2.0, 1.0], bc_path("3d/bridge.bc")
+    o = oracle_mod.OracleSim([0, 0, 0], dom, grid)
+    o.read_material(MATERIAL)
+    rho = np.random.default_rng(88).uniform(0, 1, o.ne)
+    o.set_densities(rho)
+    o.apply_bc_file(bc)
+    o.set_simp(1.0, 1e-4, 3.0)
+    o.mg_create(levels)
+    f, dm = o.load_vector(), o.mg_level_dmask(0).astype(bool)
+    want = {tol: o.mg_pcg(np.zeros_like(f), f, 100, tol, 1, 2, True) for tol in (1e-4, 1e-10)}
+    comms, hs = make_thread_comms(world), ThreadHostSum(world)
+
+    def body(r):
+        s = SlabSolver(grid, np.zeros(3), np.array(dom), levels, r, world, comms[r], hs.bind(r), MATERIAL)
+        L = s.layout
+        s.tps.setElementDensities(rho[L.elem_slice()].copy())
+        s.apply_bc_file(bc)
+        s.tps.E_0, s.tps.E_min, s.tps.gamma = 1.0, 1e-4, 3.0
+        np.testing.assert_array_equal(s.tps.buildLoadVector(), f[L.node_slice()])
+        np.testing.assert_array_equal(s.tps.dirichletMask, dm[L.node_slice()])
+        mg = s.multigrid()
+        fl = s.tps.buildLoadVector()
+        for tol in (1e-4, 1e-10):
+            uo, no, _ = want[tol]
+            u, n, _ = mg.preconditionedConjugateGradient(np.zeros_like(fl), fl, 100, tol, mgIterations=1, mgSmoothingIterations=2,
+                                                         fullMultigrid=True, return_info=True)
+            assert n == no, (tol, n, no)
+            if tol == 1e-10:
+                rows, grow = L.owned_node_rows(), L.owned_global_node_rows()
+                assert np.max(np.abs(u[rows] - uo[grow])) / np.max(np.abs(uo)) < 1e-8
+    run_ranks(world, body)
