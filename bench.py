@@ -344,7 +344,15 @@ def our_arm(args):
 
     # ---- headline workload: weak scaling, one 128x64x64 block of element layers per GPU, slabs along axis 0 ----
     gE = [GRID[0] * world, GRID[1], GRID[2]]
-    wl = Workload(V, S, torch, dist, gE, [DOMAIN[0] * world, DOMAIN[1], DOMAIN[2]], BC, args.levels, rank, world, local, "flat")
+    # coarsening levels: the reference's production value 3 (fem.py --mgl 3); the weak-scaling grid grows along axis 0, and with
+    # it the plane chain of the coarsest direct solve, so the hierarchy is deepened until the coarsest grid has <= 64 layers
+    # (N = 8: 4 levels; measured 46.0 ms per solve against 66.9 ms with 3, same 10 iterations - profiles/r02c_weak_levels_n8.txt)
+    levels = args.levels
+    if levels <= 0:
+        levels = 3
+        while (gE[0] >> levels) > 64 and (GRID[0] % (1 << (levels + 1))) == 0 and min(GRID[1], GRID[2]) % (1 << (levels + 1)) == 0:
+            levels += 1
+    wl = Workload(V, S, torch, dist, gE, [DOMAIN[0] * world, DOMAIN[1], DOMAIN[2]], BC, levels, rank, world, local, "flat")
     sampler = ClockSampler(local); sampler.start()
     ms, kms, launches, nsets, bufs = time_kapply(L, torch, dist, wl, W, K, 89 + rank)
     clocks = sampler.stop()
@@ -547,7 +555,7 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--levels", type=int, default=3)
+    ap.add_argument("--levels", type=int, default=0, help="coarsening levels of the headline solve (0 = 3, deepened for long weak-scaling grids)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-solve", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
