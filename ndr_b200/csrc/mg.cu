@@ -188,7 +188,14 @@ void MG<N>::updateElementStiffnessMatrices(bool force) {
     }
     for (size_t l = 2; l <= L; ++l) {
         long long tot = (long long)lv[l].g.nn * NST;
-        galerkinStencilKernel<N><<<unsigned((tot + kBlock - 1) / kBlock), kBlock, 0, stream>>>(lv[l - 1].g, lv[l].g, lv[l - 1].S.p, lv[l].S.p);
+        static const bool threadForm = getenv("VFEM_GALERKIN_THREAD") != nullptr; // the round-1 kernel (thread per output block), for comparison
+        if (threadForm) galerkinStencilKernel<N><<<unsigned((tot + kBlock - 1) / kBlock), kBlock, 0, stream>>>(lv[l - 1].g, lv[l].g, lv[l - 1].S.p, lv[l].S.p);
+        else {
+            constexpr size_t smem = size_t(NST) * N * NST * N * sizeof(Real);
+            static bool attr = false;
+            if (!attr) { VFEM_CUDA(cudaFuncSetAttribute(galerkinStencilCtaKernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem))); attr = true; }
+            galerkinStencilCtaKernel<N><<<unsigned(lv[l].g.nn), 256, smem, stream>>>(lv[l - 1].g, lv[l].g, lv[l - 1].S.p, lv[l].S.p);
+        }
         VFEM_CHECK_LAUNCH(); countLaunch();
     }
     // coarsest level: block-tridiagonal LDL^T of the Dirichlet-reduced operator (coarse_solve.cuh).  Slab mode: the
