@@ -164,6 +164,35 @@ def test_oc_50_iterations_vs_oracle(oracle_mod):
     print("50 OC steps: worst max-abs density difference %.3e" % worst)
 
 
+def test_config2_oc_iterations_vs_oracle(oracle_mod):
+    """BASELINE configs[1] at its full size, 128x64x64, with the production solver settings of fem.py (tol 1e-4, FMG, 2 sweeps,
+    warm start): the design after each of 8 optimality-criterion iterations against the oracle, max-abs density <= 1e-8
+    (north_star) - the two sides run the same PCG iterations, so they agree far below the solver tolerance."""
+    import ndr_b200.pyVoxelFEM as V
+    grid, vol = [128, 64, 64], 0.4
+    o, g = pair(oracle_mod, [2, 1, 1], grid, "3d/cantilever_flexion.bc", np.full(int(np.prod(grid)), vol))
+    o.mg_create(3)
+    o.top_create(True, vol, [("smoothing", 1), ("projection", 1.0)])
+    o.top_set_solver(100, 1e-4, 1, 2, True, False)
+    obj = V.MultigridComplianceObjective(g.multigridSolver(3))
+    top = V.TopologyOptimizationProblem(g, obj, [V.TotalVolumeConstraint(vol)], [V.SmoothingFilter(), V.ProjectionFilter()])
+    obj.tol = 1e-4
+    x0 = np.full(o.ne, vol)
+    o.top_set_vars(x0); top.setVars(x0)
+    oc = V.OCOptimizer(top)
+    worst = 0.0
+    for step in range(8):
+        lam_o, _ = o.oc_step()
+        oc.step()
+        assert abs(oc.lastLambda - lam_o) <= 1e-9 * lam_o, step
+        d = float(np.max(np.abs(top.getVars() - o.top_vars(0))))
+        worst = max(worst, d)
+        assert d <= 1e-8, (step, d)
+        Jo = o.top_objective()
+        assert abs(top.evaluateObjective() - Jo) <= 1e-9 * Jo, step
+    print("config 2, 8 OC steps: worst max-abs density difference %.3e" % worst)
+
+
 def test_config2_50_oc_iterations_trajectory():
     """BASELINE configs[1] "50 OC iterations" at 128x64x64, GPU only (fem.py protocol, tol 1e-4): the compliance
     trajectory is compared with the committed one (tests/golden/config2_oc50_gpu.json, written by the first run of this
