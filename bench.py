@@ -254,10 +254,12 @@ def time_kapply(L, torch, dist, wl, W, K, seed, preheat_s=0.3):
     launches0 = L.vfem_launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
+    t_issue = time.perf_counter()
     run(W, K)
+    t_issue = (time.perf_counter() - t_issue) * 1e3 / K   # host time to ENQUEUE one step (N > 1: includes the in-flight bound's waits)
     ev1.record()
     sync_all()
-    trace("timed region done")
+    trace("timed region done; host issue %.1f us per step" % (t_issue * 1e3))
     ms = ev0.elapsed_time(ev1)
     launches = L.vfem_launch_count() - launches0
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")

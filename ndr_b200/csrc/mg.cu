@@ -136,6 +136,9 @@ MG<N>::~MG() {
     if (haloStream) cudaStreamDestroy(haloStream);
     if (haloFork) cudaEventDestroy(haloFork);
     if (haloJoin) cudaEventDestroy(haloJoin);
+    if (haloStream2) cudaStreamDestroy(haloStream2);
+    if (haloShifted) cudaEventDestroy(haloShifted);
+    if (haloJoin2) cudaEventDestroy(haloJoin2);
 }
 
 template <int N>
@@ -340,8 +343,24 @@ void MG<N>::exchangeApplyFineBody(Real *u, const Real *b, Real *out) {
     sim->template applyFineRange<MODE>(u, b, mask, out, below ? o0 : 0, above ? o1 : E0, stream, (below ? 1 : 0) | (above ? 2 : 0));
     mark("interior apply", stream);
     // the thin boundary views follow the shift on ITS stream: they share the SMs with the tail of the interior launch
+    // a middle rank has two of them: the second one runs beside the first on a stream of its own (they write disjoint planes)
+    static const bool serialViews = getenv("VFEM_HALO_SERIAL_VIEWS") != nullptr;
+    const bool split = below && above && hs != stream && !serialViews && !traceHalo;
+    if (split) {
+        if (!haloStream2) {
+            VFEM_CUDA(cudaStreamCreateWithFlags(&haloStream2, cudaStreamNonBlocking));
+            VFEM_CUDA(cudaEventCreateWithFlags(&haloShifted, cudaEventDisableTiming));
+            VFEM_CUDA(cudaEventCreateWithFlags(&haloJoin2, cudaEventDisableTiming));
+        }
+        VFEM_CUDA(cudaEventRecord(haloShifted, hs));
+        VFEM_CUDA(cudaStreamWaitEvent(haloStream2, haloShifted, 0));
+    }
     if (below) sim->template applyFineRange<MODE>(u, b, mask, out, o0 - 1, o0 + 1, hs, 3);
-    if (above) sim->template applyFineRange<MODE>(u, b, mask, out, o1 - 1, o1 + 1, hs, 3);
+    if (above) sim->template applyFineRange<MODE>(u, b, mask, out, o1 - 1, o1 + 1, split ? haloStream2 : hs, 3);
+    if (split) {
+        VFEM_CUDA(cudaEventRecord(haloJoin2, haloStream2));
+        VFEM_CUDA(cudaStreamWaitEvent(stream, haloJoin2, 0));
+    }
     mark("boundary views", hs);
     if (hs != stream) {
         VFEM_CUDA(cudaEventRecord(haloJoin, hs));

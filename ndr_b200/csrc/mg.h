@@ -44,6 +44,8 @@ struct MG : MGBase {
     int coarseP = 0, coarsePlanes = 0;
     cudaStream_t haloStream = nullptr; // slab mode: the fine-level halo shift runs here, behind the interior K-apply
     cudaEvent_t haloFork = nullptr, haloJoin = nullptr;
+    cudaStream_t haloStream2 = nullptr; // the second boundary view of a middle rank runs beside the first one
+    cudaEvent_t haloShifted = nullptr, haloJoin2 = nullptr;
     unsigned long long builtVersion = 0;
     bool symmetricGS = true;                       // MG.hh:758
     bool buildBlockStiffnessMatrices = true;       // MG.hh:746 (kept for API parity; no effect on results)

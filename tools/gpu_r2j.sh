@@ -8,7 +8,7 @@ TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr
 ( time timeout 400 $TR --master-port 29701 bench.py --gpus $N --steps 20 --warmup 5 ) > $O/bench_full.out 2> $O/bench_full.err; echo "rc=$?" >> $O/bench_full.err
 if grep -q "rc=0" $O/bench_full.err; then
 ( time timeout 200 $TR --master-port 29702 bench.py --impl reference --gpus $N --steps 5 --warmup 3 ) > $O/bench_ref.out 2> $O/bench_ref.err; echo "rc=$?" >> $O/bench_ref.err
-( time VFEM_HALO_GRAPH=1 timeout 200 $TR --master-port 29703 bench.py --gpus $N --steps 20 --warmup 5 --no-extra --no-solve ) > $O/bench_apply_halograph.out 2> $O/bench_apply_halograph.err; echo "rc=$?" >> $O/bench_apply_halograph.err
+[ -z "$SKIP_HALO_GRAPH" ] && ( time VFEM_HALO_GRAPH=1 timeout 200 $TR --master-port 29703 bench.py --gpus $N --steps 20 --warmup 5 --no-extra --no-solve ) > $O/bench_apply_halograph.out 2> $O/bench_apply_halograph.err; echo "rc=$?" >> $O/bench_apply_halograph.err
 fi
 grep "rc=\|^real" $O/*.err | tr '\n' ' '; echo
 for f in $O/bench*.out; do echo $f; python - "$f" <<'P'
