@@ -99,7 +99,11 @@ struct BlockTri {
             void *args[] = {&Pv, &ci, &trm, &tcm, &sinv, &b, &dmask, &x, &zp};
             const size_t smem = size_t(2) * P * sizeof(Real);
             if (smem > 48 * 1024) VFEM_CUDA(cudaFuncSetAttribute(blockTriChainGridKernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-            VFEM_CUDA(cudaLaunchCooperativeKernel((const void *)blockTriChainGridKernel<N>, dim3(chainGridBlocks), dim3(kChainGridThreads), args, smem, stream));
+            // a forward / backward step has 2 P rows (two chains): enough warps for one row each where the CTA size allows it
+            int threads = kChainGridThreads;
+            while (threads < kChainGridMaxThreads && chainGridBlocks * (threads / 32) < 2 * P) threads += 128;
+            if (const char *v = getenv("VFEM_CHAIN_GRID_THREADS")) threads = std::max(64, std::min(kChainGridMaxThreads, atoi(v) / 32 * 32));
+            VFEM_CUDA(cudaLaunchCooperativeKernel((const void *)blockTriChainGridKernel<N>, dim3(chainGridBlocks), dim3(threads), args, smem, stream));
         }
         countLaunch();
     }

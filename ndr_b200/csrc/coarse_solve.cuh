@@ -217,23 +217,23 @@ static __global__ void __launch_bounds__(kChainThreads) blockTriChainKernel(int 
 // with ld.global.cg: other CTAs wrote them in the previous step); a grid barrier per chain step.  A lane issues all its
 // loads of a row (up to 32) before the first multiply, so a step costs about one memory round trip, and the rows of the
 // next step are prefetched into L2 before the barrier.  Dynamic shared memory: P doubles.
-constexpr int kChainGridThreads = 256;
+constexpr int kChainGridThreads = 256, kChainGridMaxThreads = 384; // default / upper bound of the CTA size (block_tri.h picks it: a warp per row of a step where that fits)
 template <int N>
-static __global__ void __launch_bounds__(kChainGridThreads) blockTriChainGridKernel(int P, ChainIdx ci, const Real *__restrict__ Trm,
+static __global__ void __launch_bounds__(kChainGridMaxThreads) blockTriChainGridKernel(int P, ChainIdx ci, const Real *__restrict__ Trm,
                                                                                 const Real *__restrict__ Tcm, const Real *__restrict__ Sinv,
                                                                                 const Real *__restrict__ b, const uint8_t *__restrict__ dmask,
                                                                                 Real *x, Real *z) {
     namespace cg = cooperative_groups;
     cg::grid_group grid = cg::this_grid();
     extern __shared__ Real sv[]; // [chain][P]
-    const int lane = threadIdx.x & 31, gtid = blockIdx.x * kChainGridThreads + threadIdx.x, gthreads = gridDim.x * kChainGridThreads;
+    const int lane = threadIdx.x & 31, gtid = blockIdx.x * blockDim.x + threadIdx.x, gthreads = gridDim.x * blockDim.x;
     const int gw = gtid >> 5, tw = gthreads >> 5;
     const int planes = ci.planes, mid = ci.mid, S = ci.steps();
     const size_t PP = size_t(P) * P;
     auto masked = [&](int dof, Real v) { return ((dmask[dof / N] >> (dof % N)) & 1u) ? 0.0 : v; };
     auto stage = [&](const Real *v0, const Real *v1) { // plane vectors of both chains -> shared memory (block-wide)
         __syncthreads();
-        for (int i = threadIdx.x; i < P; i += kChainGridThreads) { sv[i] = v0 ? __ldcg(v0 + i) : 0.0; sv[P + i] = v1 ? __ldcg(v1 + i) : 0.0; }
+        for (int i = threadIdx.x; i < P; i += blockDim.x) { sv[i] = v0 ? __ldcg(v0 + i) : 0.0; sv[P + i] = v1 ? __ldcg(v1 + i) : 0.0; }
         __syncthreads();
     };
     auto rowDot = [&](const Real *__restrict__ row, const Real *v) { // row . v (v in shared memory), all lanes return the sum
