@@ -78,15 +78,19 @@ struct BlockTri {
                 const char *v = getenv("VFEM_CHAIN_CLUSTER");
                 const int want = v ? atoi(v) : 16;
                 if (want > kChainCluster && want <= 16 &&
-                    cudaFuncSetAttribute(blockTriChainKernel<N>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
+                    cudaFuncSetAttribute(blockTriChainKernel<N, 2>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess &&
+                    cudaFuncSetAttribute(blockTriChainKernel<N, kChainSlots>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
                     cfg.gridDim = dim3(want); attr[0].val.clusterDim.x = want;
                     int n = 0;
-                    if (cudaOccupancyMaxActiveClusters(&n, blockTriChainKernel<N>, &cfg) == cudaSuccess && n >= 1) chainCluster = want;
+                    if (cudaOccupancyMaxActiveClusters(&n, blockTriChainKernel<N, 2>, &cfg) == cudaSuccess && n >= 1) chainCluster = want;
                 } else if (want >= 1 && want < kChainCluster && 2 * P <= kChainSlots * want * (kChainThreads / 32)) chainCluster = want;
                 (void)cudaGetLastError();
             }
             cfg.gridDim = dim3(chainCluster); attr[0].val.clusterDim.x = chainCluster;
-            VFEM_CUDA(cudaLaunchKernelEx(&cfg, blockTriChainKernel<N>, P, ci, (const Real *)Trm.p, (const Real *)Tcm.p, (const Real *)D.p, b, dmask, x, z.p));
+            if (2 * P <= 2 * chainCluster * (kChainThreads / 32)) // a warp per 2 rows: the instantiation without register spills
+                VFEM_CUDA(cudaLaunchKernelEx(&cfg, blockTriChainKernel<N, 2>, P, ci, (const Real *)Trm.p, (const Real *)Tcm.p, (const Real *)D.p, b, dmask, x, z.p));
+            else
+                VFEM_CUDA(cudaLaunchKernelEx(&cfg, blockTriChainKernel<N, kChainSlots>, P, ci, (const Real *)Trm.p, (const Real *)Tcm.p, (const Real *)D.p, b, dmask, x, z.p));
         } else { // large planes: the whole device, one grid barrier per chain step
             if (chainGridBlocks == 0) {
                 int dev = 0, sms = 148;

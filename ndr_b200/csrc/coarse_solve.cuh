@@ -60,7 +60,9 @@ static __global__ void setIdentityBlocksKernel(Real *__restrict__ W, int P, int 
 
 constexpr int kChainThreads = 512; // per CTA
 constexpr int kChainCluster = 8;   // portable cluster size
-constexpr int kChainSlots = 4;     // matrix rows per warp and step: 2 chains x P rows <= kChainSlots * 128 warps
+constexpr int kChainSlots = 4;     // matrix rows per warp and step at most: 2 chains x P rows <= kChainSlots * 128 warps (8 CTAs);
+                                   // the kernel is instantiated with SLOTS = 2 as well: a 16-CTA cluster has a warp per 2 rows up to P = 256, and
+                                   // 4 x 8 prefetched doubles per lane do not fit the 128 registers of a 512-thread CTA (248 bytes of spills)
 
 // Index helpers of the two-ended ("burn at both ends") elimination shared by both kernels and the host factorisation.
 // Planes 0..mid-1 are eliminated downwards (chain 0), planes-1..mid+1 upwards (chain 1), plane `mid` last.
@@ -81,7 +83,7 @@ struct ChainIdx {
 // Dynamic shared memory: 4*P doubles (current / next vector of both chains).  Requires 2 P <= 512 rows per step.
 // The matrix rows of the NEXT step are fetched into registers before the cluster barrier of the current one, so the
 // L2/HBM latency of the (vector-independent) matrices overlaps the barrier.  Larger planes: blockTriChainGridKernel.
-template <int N>
+template <int N, int SLOTS>
 static __global__ void __launch_bounds__(kChainThreads) blockTriChainKernel(int P, ChainIdx ci, const Real *__restrict__ Trm, const Real *__restrict__ Tcm,
                                                                             const Real *__restrict__ Sinv, const Real *__restrict__ b,
                                                                             const uint8_t *__restrict__ dmask, Real *x, Real *z) {
@@ -100,10 +102,10 @@ static __global__ void __launch_bounds__(kChainThreads) blockTriChainKernel(int 
         if (lane < ncta) cl.map_shared_rank(nxt, lane)[e] = v;
     };
     constexpr int JP = 8;
-    Real t[kChainSlots][JP];
-    int sc[kChainSlots], si[kChainSlots]; // chain and row of this warp's slots (-1: none)
+    Real t[SLOTS][JP];
+    int sc[SLOTS], si[SLOTS]; // chain and row of this warp's slots (-1: none)
 #pragma unroll
-    for (int k = 0; k < kChainSlots; ++k) { const int r = gw + k * tw; sc[k] = r < 2 * P ? r / P : -1; si[k] = r < 2 * P ? r - (r / P) * P : 0; }
+    for (int k = 0; k < SLOTS; ++k) { const int r = gw + k * tw; sc[k] = r < 2 * P ? r / P : -1; si[k] = r < 2 * P ? r - (r / P) * P : 0; }
     // phase 0: forward step s, 1: middle, 2: backward step s  ->  matrix block of chain c, or -1 when the chain is idle
     auto blockOf = [&](int phase, int s, int c) {
         if (phase == 0) return s <= ci.len(c) - 1 ? ci.fwdBlock(c, s) : -1;
@@ -112,16 +114,16 @@ static __global__ void __launch_bounds__(kChainThreads) blockTriChainKernel(int 
     };
     auto fetch = [&](int phase, int s) {
 #pragma unroll
-        for (int k = 0; k < kChainSlots; ++k) {
+        for (int k = 0; k < SLOTS; ++k) {
             const int q = sc[k] >= 0 ? blockOf(phase, s, sc[k]) : -1;
             const Real *row = (phase == 2 ? Tcm : Trm) + size_t(q < 0 ? 0 : q) * PP + size_t(si[k]) * P;
 #pragma unroll
             for (int j = 0; j < JP; ++j) { const int c = lane + 32 * j; t[k][j] = (q >= 0 && c < P) ? row[c] : 0.0; }
         }
     };
-    auto dots = [&](Real (&s)[kChainSlots]) {
+    auto dots = [&](Real (&s)[SLOTS]) {
 #pragma unroll
-        for (int k = 0; k < kChainSlots; ++k) {
+        for (int k = 0; k < SLOTS; ++k) {
             const Real *v = cur + (sc[k] > 0 ? P : 0);
             Real a = 0.0;
 #pragma unroll
@@ -131,14 +133,14 @@ static __global__ void __launch_bounds__(kChainThreads) blockTriChainKernel(int 
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1)
 #pragma unroll
-            for (int k = 0; k < kChainSlots; ++k) s[k] += __shfl_xor_sync(0xffffffffu, s[k], o);
+            for (int k = 0; k < SLOTS; ++k) s[k] += __shfl_xor_sync(0xffffffffu, s[k], o);
     };
     // one step of both chains; the registers already hold its matrix rows, (nphase, ns) names the step to prefetch
     auto chainStep = [&](int phase, int s, int nphase, int ns) {
-        Real d[kChainSlots];
+        Real d[SLOTS];
         dots(d);
 #pragma unroll
-        for (int k = 0; k < kChainSlots; ++k) {
+        for (int k = 0; k < SLOTS; ++k) {
             if (sc[k] < 0) continue;
             const int c = sc[k], i = si[k], e = c * P + i;
             if (blockOf(phase, s, c) < 0) { publish(e, phase == 1 ? 0.0 : cur[e]); continue; } // idle chain: keep its vector
