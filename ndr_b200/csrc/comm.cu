@@ -48,148 +48,14 @@ NcclApi &nccl() {
         if (r_ != ncclSuccess) throw std::runtime_error(std::string("NCCL error: ") + nccl().GetErrorString(r_) + " at " + __FILE__ + ":" + std::to_string(__LINE__)); \
     } while (0)
 
-// ---- halo shift through NVLink peer memory ---------------------------------------------------------------------------
-// OPT-IN (VFEM_PEER_HALO=1): measured on 2 B200 it is SLOWER than NCCL's LL protocol for these 100 KB planes (about 20 us
-// against 12 us per shift inside a GS sweep, profiles/r01m_peer_halo.txt), because the data + flag + acknowledgement chain
-// pays three system-scope fences over NVLink; it stays as the base for fusing the push into the producing kernel.
-// Every rank owns a MAILBOX in its HBM, mapped into its two neighbours with CUDA IPC: the sender's blocks store the plane straight into the neighbour's mailbox over NVLink, fence,
-// and the last one raises the neighbour's sequence flag; the receiver's blocks (same launch on that rank) wait for the
-// flag, move the plane from the mailbox to the ghost plane and acknowledge.  Two slots per direction, so a sender only
-// ever waits for the acknowledgement of the message before the previous one.  Flags sit on their own 128-byte lines and
-// have exactly one writer each.
-enum PeerFlag { SEQ_FROM_BELOW, SEQ_FROM_ABOVE, ACK_FROM_BELOW, ACK_FROM_ABOVE, DONE_SEND_UP, DONE_RECV_UP, DONE_SEND_DOWN, DONE_RECV_DOWN, PEER_FLAGS };
-constexpr size_t kFlagStride = 128;
-constexpr int kPeerThreads = 256, kPeerMaxBlocks = 8;
-
-struct PeerShiftArgs {
-    const Real *sendUp, *sendDown;
-    Real *recvBelow, *recvAbove;
-    size_t count, cap;
-    unsigned char *self, *above, *below;   // mailboxes; above / below are IPC mappings (nullptr at the ends of the chain)
-    unsigned long long seqUp, seqDown;     // message numbers of this call, 0 = direction not taken
-    unsigned long long target[4];          // cumulative block count of each role after this call
-    int nblk;
-    int *err;
-};
-
-__device__ inline unsigned long long *peerFlag(unsigned char *box, int f) { return reinterpret_cast<unsigned long long *>(box + size_t(f) * kFlagStride); }
-__device__ inline Real *peerData(unsigned char *box, int fromAbove, unsigned long long seq, size_t cap) {
-    return reinterpret_cast<Real *>(box + size_t(PEER_FLAGS) * kFlagStride) + (size_t(fromAbove) * 2 + (seq & 1ull)) * cap;
-}
-__device__ inline bool peerWait(unsigned long long *flag, unsigned long long want, int *err) {
-    unsigned long long t0, t, v;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-    for (;;) {
-        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flag) : "memory");
-        if (v >= want) return true;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-        if (t - t0 > 20000000000ull) { *err = 1; return false; } // 20 s: a neighbour never came - report instead of hanging the GPU
-    }
-}
-__device__ inline void peerSignal(unsigned long long *flag, unsigned long long v) {
-    __threadfence_system();
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"(v) : "memory");
-}
-
-__global__ void __launch_bounds__(kPeerThreads) peerShiftKernel(PeerShiftArgs a) {
-    const int role = blockIdx.x / a.nblk, b = blockIdx.x % a.nblk; // 0 send up, 1 receive from below, 2 send down, 3 receive from above
-    const bool upward = role < 2, sender = (role & 1) == 0;
-    const unsigned long long seq = upward ? a.seqUp : a.seqDown;
-    unsigned char *peer = sender ? (upward ? a.above : a.below) : (upward ? a.below : a.above);
-    if (!seq || !peer) return;
-    __shared__ int ok;
-    if (sender) {
-        const Real *src = upward ? a.sendUp : a.sendDown;
-        if (threadIdx.x == 0) ok = peerWait(peerFlag(a.self, upward ? ACK_FROM_ABOVE : ACK_FROM_BELOW), seq >= 2 ? seq - 2 : 0, a.err);
-        __syncthreads();
-        if (ok) {
-            Real *dst = peerData(peer, upward ? 0 : 1, seq, a.cap);
-            for (size_t i = size_t(b) * kPeerThreads + threadIdx.x; i < a.count; i += size_t(a.nblk) * kPeerThreads) dst[i] = src[i];
-        }
-        __threadfence_system();
-        __syncthreads();
-        if (threadIdx.x == 0 && atomicAdd(peerFlag(a.self, upward ? DONE_SEND_UP : DONE_SEND_DOWN), 1ull) + 1 == a.target[role])
-            peerSignal(peerFlag(peer, upward ? SEQ_FROM_BELOW : SEQ_FROM_ABOVE), seq);
-    } else {
-        Real *dst = upward ? a.recvBelow : a.recvAbove;
-        if (threadIdx.x == 0) ok = peerWait(peerFlag(a.self, upward ? SEQ_FROM_BELOW : SEQ_FROM_ABOVE), seq, a.err);
-        __syncthreads();
-        if (ok) {
-            const Real *src = peerData(a.self, upward ? 0 : 1, seq, a.cap);
-            for (size_t i = size_t(b) * kPeerThreads + threadIdx.x; i < a.count; i += size_t(a.nblk) * kPeerThreads) dst[i] = __ldcg(src + i);
-        }
-        __syncthreads();
-        if (threadIdx.x == 0 && atomicAdd(peerFlag(a.self, upward ? DONE_RECV_UP : DONE_RECV_DOWN), 1ull) + 1 == a.target[role])
-            peerSignal(peerFlag(peer, upward ? ACK_FROM_ABOVE : ACK_FROM_BELOW), seq);
-    }
-}
-
+// (Round 1's peer-memory mailbox shift - data + flag + acknowledgement over CUDA IPC - measured slower than ncclSend/ncclRecv
+// for these 100 KB planes, profiles/r01m_peer_halo.txt, and is gone; the numbers stay in the profile.)
 struct NcclComm : SlabComm {
     ncclComm_t comm = nullptr;
     bool graphs = false;
-    // peer-memory shift state
-    unsigned char *box = nullptr, *boxAbove = nullptr, *boxBelow = nullptr;
-    size_t cap = 0;
-    unsigned long long seqUp = 0, seqDown = 0, blocksDone[4] = {0, 0, 0, 0};
-    int *errHost = nullptr, *errDev = nullptr;
-    bool peer = false;
-    ~NcclComm() override {
-        if (boxAbove) cudaIpcCloseMemHandle(boxAbove);
-        if (boxBelow) cudaIpcCloseMemHandle(boxBelow);
-        if (box) cudaFree(box);
-        if (errHost) cudaFreeHost(errHost);
-        if (comm) nccl().CommDestroy(comm);
-    }
-    void preparePeer(size_t maxCount, cudaStream_t s) override {
-        if (world < 2 || peer || !getenv("VFEM_PEER_HALO")) return;
-        NcclApi &a = nccl();
-        cap = (maxCount + 15) / 16 * 16;
-        const size_t bytes = size_t(PEER_FLAGS) * kFlagStride + 4 * cap * sizeof(Real);
-        int bad = 0;
-        cudaIpcMemHandle_t mine;
-        memset(&mine, 0, sizeof mine);
-        if (cudaMalloc((void **)&box, bytes) != cudaSuccess) { box = nullptr; bad = 1; }
-        if (!bad && (cudaMemsetAsync(box, 0, bytes, s) != cudaSuccess || cudaIpcGetMemHandle(&mine, box) != cudaSuccess)) bad = 1;
-        if (cudaHostAlloc((void **)&errHost, sizeof(int), cudaHostAllocMapped) != cudaSuccess || cudaHostGetDevicePointer((void **)&errDev, errHost, 0) != cudaSuccess) bad = 1;
-        else *errHost = 0;
-        (void)cudaGetLastError();
-        static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handles are 64 bytes");
-        DevBuf<uint8_t> all(size_t(world) * 64);
-        VFEM_CUDA(cudaMemcpyAsync(all.p + size_t(rank) * 64, &mine, 64, cudaMemcpyHostToDevice, s));
-        VFEM_NCCL(a.AllGather(all.p + size_t(rank) * 64, all.p, 64, ncclUint8, comm, s)); // in place; orders every rank's memset before any neighbour's first store
-        std::vector<uint8_t> handles = all.toHost(s);
-        auto open = [&](int r, unsigned char **out) {
-            cudaIpcMemHandle_t h;
-            memcpy(&h, handles.data() + size_t(r) * 64, 64);
-            if (cudaIpcOpenMemHandle((void **)out, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { *out = nullptr; bad = 1; (void)cudaGetLastError(); }
-        };
-        if (!bad && rank + 1 < world) open(rank + 1, &boxAbove);
-        if (!bad && rank > 0) open(rank - 1, &boxBelow);
-        DevBuf<Real> flag(1);
-        const Real mineBad = bad;
-        VFEM_CUDA(cudaMemcpyAsync(flag.p, &mineBad, sizeof(Real), cudaMemcpyHostToDevice, s));
-        allreduceSum(flag.p, 1, s); // either every rank shifts through peer memory or none does
-        Real anyBad = 0;
-        flag.download(&anyBad, s);
-        peer = anyBad == 0;
-        if (!peer && rank == 0) fprintf(stderr, "ndr_b200: peer-memory halo shift unavailable (CUDA IPC failed on %d rank(s)); using ncclSend/ncclRecv\n", int(anyBad));
-    }
-    void peerShift(const Real *sendUp, Real *recvBelow, const Real *sendDown, Real *recvAbove, size_t count, bool up, bool down, cudaStream_t s) {
-        if (*errHost) throw std::runtime_error("peer-memory halo shift: a neighbouring rank did not answer within 20 s");
-        PeerShiftArgs a;
-        a.sendUp = sendUp; a.sendDown = sendDown; a.recvBelow = recvBelow; a.recvAbove = recvAbove;
-        a.count = count; a.cap = cap; a.self = box; a.above = boxAbove; a.below = boxBelow;
-        a.seqUp = up ? ++seqUp : 0; a.seqDown = down ? ++seqDown : 0;
-        a.nblk = int(std::min<size_t>(kPeerMaxBlocks, std::max<size_t>(1, count / 2048)));
-        const bool active[4] = {up && boxAbove, up && boxBelow, down && boxBelow, down && boxAbove};
-        for (int r = 0; r < 4; ++r) { if (active[r]) blocksDone[r] += a.nblk; a.target[r] = blocksDone[r]; }
-        a.err = errDev;
-        peerShiftKernel<<<4 * a.nblk, kPeerThreads, 0, s>>>(a);
-        VFEM_CHECK_LAUNCH();
-    }
+    ~NcclComm() override { if (comm) nccl().CommDestroy(comm); }
     void shift(const Real *sendUp, Real *recvBelow, const Real *sendDown, Real *recvAbove, size_t count, bool up, bool down,
                cudaStream_t s) override {
-        if (peer && count <= cap) { peerShift(sendUp, recvBelow, sendDown, recvAbove, count, up, down, s); return; }
         NcclApi &a = nccl();
         VFEM_NCCL(a.GroupStart());
         if (up) {
@@ -204,7 +70,7 @@ struct NcclComm : SlabComm {
     }
     void allreduceSum(Real *buf, size_t n, cudaStream_t s) override { VFEM_NCCL(nccl().AllReduce(buf, buf, n, ncclDouble, ncclSum, comm, s)); }
     void allreduceSumBytes(uint8_t *buf, size_t n, cudaStream_t s) override { VFEM_NCCL(nccl().AllReduce(buf, buf, n, ncclUint8, ncclSum, comm, s)); }
-    bool graphSafe() const override { return graphs && !peer; } // the peer shift numbers its messages on the host
+    bool graphSafe() const override { return graphs; }
     bool sideStreamSafe() const override { return true; }
 };
 } // namespace

@@ -25,7 +25,6 @@ struct SlabComm {
                        cudaStream_t s) = 0;
     virtual void allreduceSum(Real *buf, size_t n, cudaStream_t s) = 0;
     virtual void allreduceSumBytes(uint8_t *buf, size_t n, cudaStream_t s) = 0;
-    virtual void preparePeer(size_t /*maxCount*/, cudaStream_t) {} // collective, optional: set up a faster shift for up to maxCount doubles
     virtual bool graphSafe() const = 0; // may the calls above be captured into a CUDA graph?
     virtual bool sideStreamSafe() const = 0; // may a shift be enqueued on another stream than the solver's (overlap with compute)?
 };

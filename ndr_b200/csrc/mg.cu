@@ -21,7 +21,6 @@ MG<N>::MG(std::shared_ptr<Sim<N>> fine, size_t numCoarseningLevels, std::shared_
         useGraphs = false;
     }
     stream = fine->stream;
-    if (slab()) comm->preparePeer(size_t(fine->g.ninc[0]) * N, stream);
     useGraphs = getenv("VFEM_NO_GRAPH") == nullptr && (!slab() || comm->graphSafe());
     if (const char *v = getenv("VFEM_GS_VARIANT")) gsVariant = atoi(v);
     fusedSweeps = getenv("VFEM_NO_FUSED_SWEEPS") == nullptr;
