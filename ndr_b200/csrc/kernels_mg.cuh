@@ -151,55 +151,67 @@ static __global__ void __launch_bounds__(kBlock) galerkinStencilKernel(Grid<N> g
 // in shared memory with coalesced loads - every fine row is read by at most 2^N CTAs instead of by up to 27 x 27 threads in
 // scattered 24-byte pieces - and each warp adds up whole output blocks over the admissible (fine row, fine column) pairs
 // only: per axis the pairs (di, dj) with di + dj - 2 D in [-1, 1], 7 for D = 0 and 3 for D = +-1, weight
-// (di ? 1/2 : 1) (o ? 1/2 : 1) - the table below.  Out-of-grid fine rows are staged as zeros; out-of-grid fine columns are
+// (di ? 1/2 : 1) (o ? 1/2 : 1).  Out-of-grid fine rows are staged as zeros; out-of-grid fine columns are
 // zero entries of S_f already (every kernel that writes a stencil writes all of its slots).  Measured (gpurun r2m): operator
 // refresh 2.82 ms against 3.42 ms with the thread-per-block form above at 128x64x64, 25.2 against 27.4 ms at 256x128x128.
-struct GalerkinPairs { signed char di[13], dj[13]; Real w[13]; };
+// The admissible pairs of every output slot k are tabulated once on the host (GalerkinTable): start[k] .. start[k+1] index
+// (offset of the fine block in the staged rows, weight); 13^N entries in all.
 template <int N>
-static __global__ void __launch_bounds__(256) galerkinStencilCtaKernel(Grid<N> gf, Grid<N> gc, const Real *__restrict__ Sf, Real *__restrict__ Sc) {
-    constexpr int NST = ipow3(N), ROWLEN = N * NST * N; // doubles per node
-    extern __shared__ __align__(16) Real galSm[];        // [NST][ROWLEN]
-    __shared__ GalerkinPairs tab;
-    const int n = blockIdx.x;
-    int ci[N]; unflattenNode<N>(gc, n, ci);
-    if (threadIdx.x < 13) { // entries 0..2: D = -1, 3..9: D = 0, 10..12: D = +1
-        const signed char di[13] = {0, -1, -1, -1, -1, 0, 0, 0, 1, 1, 0, 1, 1}, dj[13] = {-1, 0, -1, 0, 1, -1, 0, 1, -1, 0, 1, 0, 1};
-        const int e = threadIdx.x, D = e < 3 ? -1 : (e < 10 ? 0 : 1), o = di[e] + dj[e] - 2 * D;
-        tab.di[e] = di[e]; tab.dj[e] = dj[e]; tab.w[e] = (di[e] ? 0.5 : 1.0) * (o ? 0.5 : 1.0);
+struct GalerkinTable {
+    static constexpr int NST = ipow3(N), ROWLEN = N * NST * N;
+    std::vector<int> start, off;
+    std::vector<Real> w;
+    GalerkinTable() {
+        const int di[13] = {0, -1, -1, -1, -1, 0, 0, 0, 1, 1, 0, 1, 1}, dj[13] = {-1, 0, -1, 0, 1, -1, 0, 1, -1, 0, 1, 0, 1}; // 0..2: D = -1, 3..9: D = 0, 10..12: D = +1
+        start.push_back(0);
+        for (int k = 0; k < NST; ++k) {
+            int D[N], cnt[N], base[N], total = 1;
+            { int tt = k; for (int d = N - 1; d >= 0; --d) { D[d] = tt % 3 - 1; tt /= 3; cnt[d] = D[d] == 0 ? 7 : 3; base[d] = D[d] == 0 ? 3 : (D[d] > 0 ? 10 : 0); total *= cnt[d]; } }
+            for (int q = 0; q < total; ++q) {
+                int rem = q, ki = 0, kj = 0, p3 = 1; Real wt = 1.0;
+                for (int d = N - 1; d >= 0; --d) { // axis N-1 is the least significant digit of a stencil slot
+                    const int x = base[d] + rem % cnt[d]; rem /= cnt[d];
+                    const int o = di[x] + dj[x] - 2 * D[d];
+                    ki += (di[x] + 1) * p3; kj += (dj[x] + 1) * p3; p3 *= 3; wt *= (di[x] ? 0.5 : 1.0) * (o ? 0.5 : 1.0);
+                }
+                off.push_back(ki * ROWLEN + kj * N); w.push_back(wt);
+            }
+            start.push_back(int(off.size()));
+        }
     }
-    for (int idx = threadIdx.x; idx < NST * ROWLEN; idx += blockDim.x) {
-        const int ki = idx / ROWLEN, r = idx - ki * ROWLEN;
+};
+template <int N>
+static __global__ void __launch_bounds__(256) galerkinStencilCtaKernel(Grid<N> gf, Grid<N> gc, const Real *__restrict__ Sf, Real *__restrict__ Sc,
+                                                                      const int *__restrict__ tStart, const int *__restrict__ tOff,
+                                                                      const Real *__restrict__ tW) {
+    constexpr int NST = ipow3(N), ROWLEN = N * NST * N, NN = N * N; // ROWLEN: doubles per node
+    extern __shared__ __align__(16) Real galSm[];                    // [NST][ROWLEN]
+    const int n = blockIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    int ci[N]; unflattenNode<N>(gc, n, ci);
+    for (int ki = warp; ki < NST; ki += nwarps) { // a warp stages whole fine rows: the node arithmetic is per row, not per double
         int tt = ki, fn = 0; bool ok = true;
 #pragma unroll
         for (int d = N - 1; d >= 0; --d) { const int di = tt % 3 - 1; tt /= 3; const int v = 2 * ci[d] + di; ok = ok && v >= 0 && v < gf.n[d]; fn += v * gf.ninc[d]; }
-        galSm[idx] = ok ? Sf[size_t(fn) * ROWLEN + r] : 0.0;
+        const Real *src = Sf + size_t(ok ? fn : 0) * ROWLEN;
+        for (int r = lane; r < ROWLEN; r += 32) galSm[ki * ROWLEN + r] = ok ? src[r] : 0.0;
     }
     __syncthreads();
     // warp w forms the output blocks k = w, w + 8, ...; its lanes share the admissible pairs of that block (3^a 7^b of them,
     // a + b = N), each lane accumulating all N x N entries, and a shuffle butterfly adds the lanes up (fixed order)
-    constexpr int NN = N * N;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     for (int k = warp; k < NST; k += nwarps) {
-        int cnt[N], base[N], total = 1; bool Jok = true;
+        bool Jok = true;
         { int tt = k;
 #pragma unroll
-          for (int d = N - 1; d >= 0; --d) {
-              const int D = tt % 3 - 1; tt /= 3;
-              const int v = ci[d] + D; Jok = Jok && v >= 0 && v < gc.n[d];
-              cnt[d] = D == 0 ? 7 : 3; base[d] = D == 0 ? 3 : (D > 0 ? 10 : 0); total *= cnt[d];
-          } }
+          for (int d = N - 1; d >= 0; --d) { const int D = tt % 3 - 1; tt /= 3; const int v = ci[d] + D; Jok = Jok && v >= 0 && v < gc.n[d]; } }
         Real acc[NN];
 #pragma unroll
         for (int i = 0; i < NN; ++i) acc[i] = 0.0;
         if (Jok) {
-            for (int q = lane; q < total; q += 32) {
-                int rem = q, ki = 0, kj = 0, p3 = 1; Real w = 1.0;
-#pragma unroll
-                for (int d = N - 1; d >= 0; --d) { // axis N-1 is the least significant digit of a stencil slot
-                    const int x = base[d] + rem % cnt[d]; rem /= cnt[d];
-                    ki += (tab.di[x] + 1) * p3; kj += (tab.dj[x] + 1) * p3; p3 *= 3; w *= tab.w[x];
-                }
-                const Real *blk = galSm + ki * ROWLEN + kj * N;
+            const int q1 = tStart[k + 1];
+            for (int q = tStart[k] + lane; q < q1; q += 32) {
+                const Real w = tW[q];
+                const Real *blk = galSm + tOff[q];
 #pragma unroll
                 for (int a = 0; a < N; ++a)
 #pragma unroll

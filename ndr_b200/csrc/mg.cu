@@ -196,7 +196,8 @@ void MG<N>::updateElementStiffnessMatrices(bool force) {
             constexpr size_t smem = size_t(NST) * N * NST * N * sizeof(Real);
             static bool attr = false;
             if (!attr) { VFEM_CUDA(cudaFuncSetAttribute(galerkinStencilCtaKernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem))); attr = true; }
-            galerkinStencilCtaKernel<N><<<unsigned(lv[l].g.nn), 256, smem, stream>>>(lv[l - 1].g, lv[l].g, lv[l - 1].S.p, lv[l].S.p);
+            if (!galStart.p) { GalerkinTable<N> t; galStart.upload(t.start, stream); galOff.upload(t.off, stream); galW.upload(t.w, stream); VFEM_CUDA(cudaStreamSynchronize(stream)); }
+            galerkinStencilCtaKernel<N><<<unsigned(lv[l].g.nn), 256, smem, stream>>>(lv[l - 1].g, lv[l].g, lv[l - 1].S.p, lv[l].S.p, galStart.p, galOff.p, galW.p);
         }
         VFEM_CHECK_LAUNCH(); countLaunch();
     }

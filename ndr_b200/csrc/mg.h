@@ -39,6 +39,8 @@ struct MG : MGBase {
     std::shared_ptr<Sim<N>> sim;
     std::vector<Level> lv;
     DevBuf<Real> d_C;               // 2^N coarsened reference stiffness matrices (MG.hh:644-648)
+    DevBuf<int> galStart, galOff;   // admissible (fine row, fine column) pairs of the Galerkin product per stencil slot (kernels_mg.cuh)
+    DevBuf<Real> galW;
     // coarsest level: block-tridiagonal LDL^T over the node planes of axis 0 (block_tri.h), refreshed once per density update
     std::unique_ptr<BlockTri<N>> bt;
     int coarseP = 0, coarsePlanes = 0;
